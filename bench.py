@@ -1,0 +1,391 @@
+#!/usr/bin/env python
+"""Benchmark of the PowerSGD reduce hot path (BASELINE.json metric: reduce ms/step and effective
+gradient GB/s) on the DistilBERT gradient set, compression rank 4 (BASELINE configs[1]).
+
+    python bench.py --gpus N --steps K --warmup W            # this repo's CUDA path
+    python bench.py --impl reference --gpus N ...            # the reference algorithm on the host CPUs
+
+A "step" is one ``PowerSGDReducer.reduce(grad_in, grad_out, memory_out)`` over the full gradient set
+(all ranks: same shapes, rank-specific seeded data; weak scaling).  ``value`` is the whole-job
+effective gradient bandwidth = N * 4*(E_hi+E_1) bytes / step time, with the gradients resident in HBM;
+``e2e`` is the same quantity with the gradients starting in pinned host memory and grad_out read back,
+both copies inside the timed region.  One JSON line is printed by rank 0.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import tempfile
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+METRIC = "powersgd_reduce_effective_grad_bandwidth"
+UNIT = "GB/s"
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=50)
+    ap.add_argument("--warmup", type=int, default=5)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="distilbert")
+    ap.add_argument("--rank", type=int, default=4, help="PowerSGD compression rank")
+    ap.add_argument("--no-reuse-query", action="store_true")
+    ap.add_argument("--extra-power-iterations", type=int, default=0)
+    ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--cpu-reps", type=int, default=5)
+    ap.add_argument("--skip-cpu-baseline", action="store_true")
+    ap.add_argument("--skip-e2e", action="store_true")
+    ap.add_argument("--no-phase-timing", action="store_true")
+    return ap.parse_args()
+
+
+def workload_config(args, st):
+    return {
+        "workload": f"{args.workload} gradient set ({st['n_mat']} matrices + {st['n_vec']} vectors, "
+                    f"{st['grad_bytes'] / 1e6:.1f} MB fp32), PowerSGD rank {args.rank}, "
+                    f"reuse_query={int(not args.no_reuse_query)}, power_iterations={args.extra_power_iterations} "
+                    "(BASELINE.json configs[1] gradient shapes)",
+        "compression_rank": args.rank,
+        "grad_bytes": st["grad_bytes"],
+        "algorithmic_bytes_per_step": st["algo_bytes"],
+        "communicated_bits_per_step": st["bits"],
+        "l2": "inputs (268 MB) exceed the 126 MB L2 and every step also writes 2x that, so no flush is needed",
+    }
+
+
+# ------------------------------------------------------------------------------------------------
+# CPU arm: the reference algorithm (oracle port; /root/reference is Python and cannot travel)
+# ------------------------------------------------------------------------------------------------
+def cpu_reduce_time(args, shapes, reps):
+    import torch
+
+    from oracle.powersgd_oracle import OracleReducer
+
+    cores = os.cpu_count() or 1
+    torch.set_num_threads(cores)
+    gen = torch.Generator().manual_seed(1000)
+    gin = [torch.randn(s, generator=gen) for s in shapes]
+    gout = [torch.zeros(s) for s in shapes]
+    mem = [torch.zeros(s) for s in shapes]
+    orc = OracleReducer(714, "cpu", n_power_iterations=args.extra_power_iterations,
+                        reuse_query=not args.no_reuse_query, rank=args.rank)
+    orc.reduce(gin, gout, mem)  # warm-up: also draws Q
+    times = []
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        orc.reduce(gin, gout, mem)
+        times.append(time.perf_counter() - t0)
+    times.sort()
+    return times[len(times) // 2], cores
+
+
+def run_reference(args):
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    from network_distributed_pytorch_b200 import workloads
+
+    shapes = workloads.WORKLOADS[args.workload]()
+    st = workloads.stats(shapes, args.rank)
+    reps = max(1, args.steps)
+    # bounded: a DistilBERT reduce is ~0.1-0.3 s on the host cores, cap the run at ~60 reps
+    reps = min(reps, 60)
+    # warm-up inside cpu_reduce_time is one call (it includes the Q draw); extra warm-ups as requested
+    sec, cores = cpu_reduce_time(args, shapes, reps)
+    value = st["grad_bytes"] / sec / 1e9
+    line = {
+        "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus,
+        "steps": reps, "warmup": max(1, args.warmup), "ms_per_step": sec * 1e3, "higher_is_better": True,
+        "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(args, st),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port",
+                         "sample": f"full {args.workload} gradient set, median of {reps} reduce() calls of the "
+                                   "oracle port (same torch CPU ops as upstream reducer.py), 1 process"},
+        "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+# ------------------------------------------------------------------------------------------------
+# clocks
+# ------------------------------------------------------------------------------------------------
+class ClockSampler:
+    FIELDS = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+              "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+              "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, gpu_index):
+        self.rows = []
+        self.proc = None
+        self.gpu = gpu_index
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(
+                ["nvidia-smi", "-i", str(self.gpu), f"--query-gpu={self.FIELDS}", "--format=csv,noheader,nounits",
+                 "-lms", "100"], stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
+            self.thread = threading.Thread(target=self._pump, daemon=True)
+            self.thread.start()
+        except OSError:
+            self.proc = None
+
+    def _pump(self):
+        for line in self.proc.stdout:
+            self.rows.append((time.time(), line.strip()))
+
+    def stop(self):
+        if self.proc is not None:
+            self.proc.terminate()
+            try:
+                self.proc.wait(timeout=5)
+            except subprocess.TimeoutExpired:
+                self.proc.kill()
+
+    def summary(self, t0, t1):
+        sm, mx, reasons = [], 0.0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for ts, line in self.rows:
+            if ts < t0 or ts > t1 + 0.15:
+                continue
+            parts = [p.strip() for p in line.split(",")]
+            try:
+                sm.append(float(parts[0]))
+                mx = max(mx, float(parts[1]))
+            except (ValueError, IndexError):
+                continue
+            for name, val in zip(names, parts[3:7]):
+                if val.lower().startswith("active"):
+                    reasons.add(name)
+        sm.sort()
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": sorted(reasons),
+                "samples": len(sm)}
+
+
+# ------------------------------------------------------------------------------------------------
+# GPU arm
+# ------------------------------------------------------------------------------------------------
+def padded_views(flat, shapes):
+    """Views of `flat` with every tensor starting on a 16-byte boundary (identical host/device layout)."""
+    views, off = [], 0
+    for s in shapes:
+        k = 1
+        for d in s:
+            k *= d
+        views.append(flat[off : off + k].view(s))
+        off += (k + 3) // 4 * 4
+    return views
+
+
+def padded_total(shapes):
+    off = 0
+    for s in shapes:
+        k = 1
+        for d in s:
+            k *= d
+        off += (k + 3) // 4 * 4
+    return off
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    from network_distributed_pytorch_b200 import _lib, workloads
+    from network_distributed_pytorch_b200.reducer import PowerSGDReducer
+
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py: no CUDA device; the B200 arm has no CPU fallback (use --impl reference)")
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("launch N>1 with: python -m torch.distributed.run --nproc-per-node N bench.py --gpus N")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    else:
+        f = tempfile.NamedTemporaryFile(delete=False)
+        f.close()
+        os.unlink(f.name)
+        dist.init_process_group("gloo", init_method="file://" + f.name, world_size=1, rank=0)
+
+    shapes = workloads.WORKLOADS[args.workload]()
+    st = workloads.stats(shapes, args.rank)
+    total = padded_total(shapes)
+    gen = torch.Generator(device=dev).manual_seed(1000 + rank)
+    in_flat = torch.randn(total, device=dev, generator=gen)
+    out_flat = torch.zeros(total, device=dev)
+    mem_flat = torch.zeros(total, device=dev)
+    gin, gout, mem = padded_views(in_flat, shapes), padded_views(out_flat, shapes), padded_views(mem_flat, shapes)
+
+    red = PowerSGDReducer(714, dev, 0, not args.no_reuse_query, args.rank,
+                          extra_power_iterations=args.extra_power_iterations)
+    lib = _lib.load()
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    W = max(3, args.warmup)
+    K = max(1, args.steps)
+    for _ in range(W):
+        red.reduce(gin, gout, mem)
+    plan = next(iter(red._plans.values()))
+    if not args.no_phase_timing:
+        plan.timing_enable(True)
+        plan.timing_read()
+
+    sampler = ClockSampler(local) if rank == 0 else None
+    if sampler:
+        sampler.start()
+        time.sleep(0.25)
+
+    # ---- timed region: K steps, device events on the launch stream, max over ranks --------------
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    barrier()
+    launches0 = lib.psgd_launch_count()
+    t_wall0 = time.time()
+    ev0.record()
+    for _ in range(K):
+        red.reduce(gin, gout, mem)
+    ev1.record()
+    barrier()
+    t_wall1 = time.time()
+    launches = lib.psgd_launch_count() - launches0
+    ms = ev0.elapsed_time(ev1)
+    phases = plan.timing_read() if not args.no_phase_timing else {}
+    plan.timing_enable(False)
+    tmax = torch.tensor([ms], device=dev)
+    if world > 1:
+        dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+    ms = float(tmax.item())
+
+    # ---- clocks: if the timed region was too short for a sample, probe under the same load -------
+    clocks = None
+    if sampler:
+        clocks = sampler.summary(t_wall0, t_wall1)
+        clocks["window"] = "timed region"
+    if world > 1 or (clocks is not None and clocks["samples"] < 3):
+        p0 = time.time()
+        while time.time() - p0 < 1.5:
+            for _ in range(20):
+                red.reduce(gin, gout, mem)
+            torch.cuda.synchronize()
+        p1 = time.time()
+        if sampler and clocks["samples"] < 3:
+            clocks = sampler.summary(p0 + 0.3, p1)
+            clocks["window"] = "1.5 s probe of the same steps right after the timed region"
+    barrier()
+
+    # ---- e2e: gradients start in pinned host memory, grad_out is read back ------------------------
+    e2e = None
+    if not args.skip_e2e:
+        host_in = torch.empty(total, dtype=torch.float32, pin_memory=True)
+        host_out = torch.empty(total, dtype=torch.float32, pin_memory=True)
+        host_in.copy_(in_flat)
+        E = max(1, args.e2e_steps)
+        for _ in range(2):
+            in_flat.copy_(host_in, non_blocking=True)
+            red.reduce(gin, gout, mem)
+            host_out.copy_(out_flat, non_blocking=True)
+        barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(E):
+            in_flat.copy_(host_in, non_blocking=True)       # H2D of this step's gradients
+            red.reduce(gin, gout, mem)                      # public API call
+            host_out.copy_(out_flat, non_blocking=True)     # D2H of the step's result (grad_out)
+        e1.record()
+        barrier()
+        ems = torch.tensor([e0.elapsed_time(e1)], device=dev)
+        if world > 1:
+            dist.all_reduce(ems, op=dist.ReduceOp.MAX)
+        ems = float(ems.item()) / E
+        e2e = {"value": world * st["grad_bytes"] / (ems * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": ems,
+               "steps": E, "h2d_bytes_per_step": total * 4, "d2h_bytes_per_step": total * 4,
+               "path": "pinned host -> HBM copy, PowerSGDReducer.reduce(), grad_out HBM -> pinned host"}
+    if sampler:
+        sampler.stop()
+
+    if rank != 0:
+        if world > 1:
+            dist.destroy_process_group()
+        return
+
+    ms_per_step = ms / K
+    value = world * st["grad_bytes"] / (ms_per_step * 1e-3) / 1e9
+
+    # ---- roofline of the dominant kernel (finalize: reads M, P, Q; writes out and mem) -----------
+    peaks_path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(peaks_path):
+        peak, peak_src = float(json.load(open(peaks_path))["hbm_gbs"]), "MEASURED_PEAKS.json hbm_gbs (measured copy)"
+    else:
+        peak, peak_src = 6650.0, "fallback of B200_PROFILING.md (MEASURED_PEAKS.json absent)"
+    roofline, phase_report = None, {}
+    algo = {"pack": st["e_1"] * 8, "p_from_m": st["k1_bytes"], "orthogonalize": st["k2_bytes"],
+            "q_from_mt": st["k3_bytes"], "q_reduce": 8 * st["e_q"], "finalize": st["k4_bytes"], "finish": st["e_1"] * 8}
+    kernel_ms = 0.0
+    for name, (msum, cnt) in phases.items():
+        if cnt:
+            avg = msum / cnt
+            calls_per_step = cnt / K
+            kernel_ms += avg * calls_per_step
+            phase_report[name] = {"ms": round(avg, 5), "GBps": round(algo[name] / (avg * 1e-3) / 1e9, 1),
+                                  "calls_per_step": calls_per_step}
+    if "finalize" in phase_report:
+        avg = phases["finalize"][0] / phases["finalize"][1]
+        achieved = st["k4_bytes"] / (avg * 1e-3) / 1e9
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "ncu_traffic.json")
+        if os.path.exists(tpath):
+            traffic = json.load(open(tpath)).get(f"k_finalize:{args.workload}:r{args.rank}")
+        roofline = {"bound": "hbm", "kernel": "k_finalize (out = P Q^T, mem = M - out)", "achieved": achieved,
+                    "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                    "algorithmic_bytes_per_launch": st["k4_bytes"], "ms_per_launch": avg, "peak_source": peak_src,
+                    "all_kernels": {"ms_per_step": kernel_ms,
+                                    "achieved": st["algo_bytes"] / (kernel_ms * 1e-3) / 1e9 if kernel_ms else None,
+                                    "frac": st["algo_bytes"] / (kernel_ms * 1e-3) / 1e9 / peak if kernel_ms else None}}
+
+    cpu = None
+    if world == 1 and not args.skip_cpu_baseline:
+        sec, cores = cpu_reduce_time(args, shapes, max(1, args.cpu_reps))
+        cpu = {"value": st["grad_bytes"] / sec / 1e9, "unit": UNIT, "cores": cores, "kind": "port",
+               "ms_per_step": sec * 1e3,
+               "sample": f"full {args.workload} gradient set, median of {max(1, args.cpu_reps)} reduce() calls of the "
+                         "oracle port (same torch CPU ops as upstream reducer.py)"}
+
+    line = {
+        "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
+        "dtype": "f32", "data": "synthetic", "config": workload_config(args, st),
+        "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
+        "clocks": clocks, "phases": phase_report,
+        "algorithmic_GBps": world * st["algo_bytes"] / (ms_per_step * 1e-3) / 1e9,
+        "hbm_roofline_frac_whole_step": st["algo_bytes"] / (ms_per_step * 1e-3) / 1e9 / peak,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -1,0 +1,127 @@
+/* psgd_b200.h -- C ABI of the B200-native PowerSGD reducer hot path.
+ *
+ * The upstream project (jaeyong-song/network_distributed_pytorch) has no FFI of its own:
+ * its boundary is the Python class PowerSGDReducer in
+ * ddp_powersgd_guide_cifar10/reducer.py (identical copy under
+ * ddp_powersgd_distillBERT_IMDb/).  Each entry point below replaces the Python loop cited
+ * next to it; the host mirror in network_distributed_pytorch_b200/reducer.py calls them
+ * through ctypes with raw device pointers and the current CUDA stream.
+ *
+ * Conventions
+ *   - every function returns 0 on success, non-zero on failure; psgd_last_error() then
+ *     holds a human readable message (thread local);
+ *   - all gradient data is fp32, row-major, contiguous; "matrix i" is the i-th tensor with
+ *     more than one dimension viewed as n[i] x m[i] (reducer.py:72-76), "vector j" the j-th
+ *     tensor with at most one dimension (reducer.py:53-57);
+ *   - p_mem / q_mem use the upstream packed layout: matrix i's P is n[i] x r[i] row-major
+ *     at element offset sum_{k<i} n[k]*r[k], Q is m[i] x r[i] at sum_{k<i} m[k]*r[k],
+ *     r[i] = min(n[i], m[i], rank), no padding (reducer.py:78-98);
+ *   - a plan is not thread safe; different plans may be used concurrently; all calls on
+ *     one plan must be issued to one stream at a time;
+ *   - `psgd_stream` is a cudaStream_t passed as void*.
+ */
+#ifndef PSGD_B200_H
+#define PSGD_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct psgd_plan psgd_plan;
+typedef struct psgd_tb psgd_tb;
+typedef void* psgd_stream;
+
+#define PSGD_ABI_VERSION 1
+#define PSGD_MAX_RANK 32
+
+/* phases, used by the tile and timing queries */
+enum {
+  PSGD_PHASE_PACK = 0,      /* K6a */
+  PSGD_PHASE_P_FROM_M = 1,  /* K1  */
+  PSGD_PHASE_ORTH = 2,      /* K2  */
+  PSGD_PHASE_Q_FROM_MT = 3, /* K3 stage 1 */
+  PSGD_PHASE_Q_REDUCE = 4,  /* K3 stage 2 */
+  PSGD_PHASE_FINALIZE = 5,  /* K4+K5 */
+  PSGD_PHASE_FINISH = 6,    /* K6b (+ in-place Q mean) */
+  PSGD_N_PHASES = 7
+};
+
+int psgd_abi_version(void);
+const char* psgd_last_error(void);
+
+/* Replaces the size pass and view construction of reducer.py:69-98 (done once per shape
+ * set instead of every call).  n/m: the 2-D views of the matrices; vec_len: element
+ * counts of the <=1-D tensors (tensor_buffer.py:10-16 prefix sums).  device >= 0 selects
+ * the CUDA device and uploads the tables; device < 0 builds the host-side plan only
+ * (no CUDA call is made; compute entry points then fail) so the layout can be inspected
+ * on a machine without a GPU. */
+int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank,
+                     int n_vec, const int64_t* vec_len, int device, psgd_plan** out);
+int psgd_plan_destroy(psgd_plan* plan);
+
+/* layout queries (host only) */
+int64_t psgd_p_elems(const psgd_plan* plan);         /* sum n*r  (reducer.py:79) */
+int64_t psgd_q_elems(const psgd_plan* plan);         /* sum m*r  (reducer.py:80) */
+int64_t psgd_vec_elems(const psgd_plan* plan);       /* tensor_buffer.py:10-13    */
+int64_t psgd_workspace_bytes(const psgd_plan* plan); /* scratch for psgd_q_from_mt */
+/* out[0..7] = n, m, r, p_off, q_off, ws_off, k3 row blocks, k3 columns per tile */
+int psgd_matrix_info(const psgd_plan* plan, int i, int64_t* out8);
+int psgd_tile_count(const psgd_plan* plan, int phase);
+/* out[0..5] = matrix, row0, nrows, col0, ncols, row-block index */
+int psgd_tile_get(const psgd_plan* plan, int phase, int idx, int32_t* out6);
+
+/* Per-step pointer refresh: parameter.grad is re-allocated by zero_grad()
+ * (ddp_init.py:144), so addresses may move every step.  Host arrays of device pointers,
+ * n_mat / n_vec entries each.  grad / err may be NULL unless fuse_add is used. */
+int psgd_set_ptrs(psgd_plan* plan, const void* const* mat_in, void* const* mat_out,
+                  void* const* mat_mem, const void* const* vec_in, void* const* vec_out,
+                  const void* const* grad, const void* const* err, psgd_stream stream);
+
+/* K6a: flat = cat(vec_in)             (tensor_buffer.py:19, reducer.py:131) */
+int psgd_pack_vec(psgd_plan* plan, float* flat, psgd_stream stream);
+/* K1: P_i = M_i Q_i for every matrix  (reducer.py:121-123).  fuse_add != 0 first forms
+ * M = grad + err (ddp_init.py:155-157) and stores it to mat_in.  q_div divides Q while it
+ * is staged (1 for the normal path; the worker count when Q still holds an all-reduce
+ * SUM, used by extra power iterations). */
+int psgd_p_from_m(psgd_plan* plan, float* p_mem, const float* q_mem, int fuse_add,
+                  float q_div, psgd_stream stream);
+/* K2: p_mem /= n_workers then modified Gram-Schmidt of every P_i in place
+ * (reducer.py:128, 136-137, 180-191). */
+int psgd_orthogonalize(psgd_plan* plan, float* p_mem, float n_workers, psgd_stream stream);
+/* K3: Q_i = M_i^T P_i                 (reducer.py:140-142): split-n partials into
+ * `workspace` (psgd_workspace_bytes, 16-byte aligned) then a fixed-order sum. */
+int psgd_q_from_mt(psgd_plan* plan, const float* p_mem, float* q_mem, void* workspace,
+                   psgd_stream stream);
+/* K4+K5: out_i = P_i (Q_i / n_workers)^T ; mem_i = M_i - out_i   (reducer.py:147,158-163).
+ * q_mem itself is left untouched (still the SUM); psgd_finish scales it. */
+int psgd_finalize(psgd_plan* plan, const float* p_mem, const float* q_mem, float n_workers,
+                  psgd_stream stream);
+/* K6b: vec_out_j = flat_j / n_workers (reducer.py:167-168, tensor_buffer.py:34-36) and, if
+ * q_mem != NULL, q_mem /= n_workers in place (reducer.py:147). */
+int psgd_finish(psgd_plan* plan, const float* flat, float* q_mem, float n_workers,
+                psgd_stream stream);
+
+/* per-phase device timing with CUDA events on the launch stream (bench.py roofline) */
+int psgd_timing_enable(psgd_plan* plan, int on);
+/* synchronises the recorded events; ms_sum/count have PSGD_N_PHASES entries; resets */
+int psgd_timing_read(psgd_plan* plan, double* ms_sum, int64_t* count);
+/* kernels launched through this library since load (all plans) */
+int64_t psgd_launch_count(void);
+
+/* Stand-alone flat packer behind tensor_buffer.TensorBuffer (tensor_buffer.py:4-36):
+ * element-size generic (1, 2, 4 or 8 bytes), layout = torch.cat of the flattened inputs. */
+int psgd_tb_create(int n, const int64_t* nelem, int elem_size, int device, psgd_tb** out);
+int psgd_tb_destroy(psgd_tb* tb);
+int psgd_tb_pack(psgd_tb* tb, const void* const* src, void* flat, psgd_stream stream);
+int psgd_tb_unpack(psgd_tb* tb, const void* flat, void* const* dst, psgd_stream stream);
+
+/* In-place modified Gram-Schmidt of one n x r row-major matrix: the module-level
+ * orthogonalize(matrix) of reducer.py:180-191. */
+int psgd_orthogonalize_one(float* mat, int64_t n, int r, int device, psgd_stream stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PSGD_B200_H */

@@ -1,0 +1,749 @@
+// C ABI of the PowerSGD hot path (see include/psgd_b200.h): host-side plan (tile tables,
+// packed offsets), per-step pointer ring and the kernel launches.
+#include <algorithm>
+#include <atomic>
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/psgd_b200.h"
+#include "psgd_kernels.cuh"
+
+using namespace psgd;
+
+namespace {
+
+thread_local std::string g_err;
+std::atomic<long long> g_launches{0};
+
+int fail(const char* fmt, ...) {
+  char buf[512];
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(buf, sizeof buf, fmt, ap);
+  va_end(ap);
+  g_err = buf;
+  return 1;
+}
+
+#define CU(call)                                                                              \
+  do {                                                                                        \
+    cudaError_t e_ = (call);                                                                  \
+    if (e_ != cudaSuccess) return fail("%s failed: %s (%s:%d)", #call, cudaGetErrorString(e_), \
+                                       __FILE__, __LINE__);                                   \
+  } while (0)
+
+long long env_ll(const char* name, long long dflt) {
+  const char* s = getenv(name);
+  if (!s || !*s) return dflt;
+  return atoll(s);
+}
+
+int pow2_ceil(long long x) {
+  int p = 1;
+  while (p < x) p <<= 1;
+  return p;
+}
+
+constexpr int kSlots = 4;
+
+struct Timer {
+  cudaEvent_t a, b;
+  int phase;
+};
+
+}  // namespace
+
+struct psgd_plan {
+  int device = -1;
+  int n_mat = 0, n_vec = 0, rank = 0, R = 1;  // R: compile-time rank the kernels run with
+  std::vector<MatDesc> mats;
+  std::vector<int4> tiles1, tiles4;
+  std::vector<ColTile> tiles3;
+  std::vector<long long> q_pre, v_pre;
+  long long p_total = 0, q_total = 0, v_total = 0, ws_total = 0;
+  int wc_cap = 0;
+  size_t smem1 = 0, smem3 = 0, smem4 = 0;
+  // device tables
+  MatDesc* d_mats = nullptr;
+  int4* d_tiles1 = nullptr;
+  int4* d_tiles4 = nullptr;
+  ColTile* d_tiles3 = nullptr;
+  long long* d_q_pre = nullptr;
+  long long* d_v_pre = nullptr;
+  // pointer ring
+  size_t slot_bytes = 0;
+  char* h_ring = nullptr;
+  char* d_ring = nullptr;
+  cudaEvent_t slot_ev[kSlots] = {};
+  bool slot_used[kSlots] = {};
+  int cur = -1;
+  PtrSlot slot{};
+  bool have_ge = false;
+  // timing
+  bool timing = false;
+  std::vector<Timer> timers;
+  std::vector<Timer> free_timers;
+  double ms_sum[PSGD_N_PHASES] = {};
+  long long ms_cnt[PSGD_N_PHASES] = {};
+};
+
+struct psgd_tb {
+  int device = -1;
+  int n = 0, elem_size = 4;
+  long long total = 0;
+  std::vector<long long> pre;
+  long long* d_pre = nullptr;
+  size_t slot_bytes = 0;
+  char* h_ring = nullptr;
+  char* d_ring = nullptr;
+  cudaEvent_t slot_ev[kSlots] = {};
+  bool slot_used[kSlots] = {};
+  int cur = 0;
+};
+
+namespace {
+
+DevPlan dev_plan(const psgd_plan* p) {
+  DevPlan d;
+  d.mats = p->d_mats;
+  d.tiles1 = p->d_tiles1;
+  d.tiles4 = p->d_tiles4;
+  d.tiles3 = p->d_tiles3;
+  d.q_pre = p->d_q_pre;
+  d.v_pre = p->d_v_pre;
+  d.n_mat = p->n_mat;
+  d.n_vec = p->n_vec;
+  d.wc_cap = p->wc_cap;
+  d.pad_ = 0;
+  return d;
+}
+
+// rows per tile for the row-streaming kernels (K1, K4)
+void build_row_tiles(const psgd_plan* p, std::vector<int4>& out, long long target_bytes, int rows_per_warp,
+                     bool single_set_when_chunked) {
+  out.clear();
+  const int gran = kWarps * rows_per_warp;
+  for (int i = 0; i < p->n_mat; ++i) {
+    const MatDesc& md = p->mats[i];
+    if (md.n == 0 || md.m == 0) continue;
+    long long t = target_bytes / ((long long)md.m * 4);
+    t = (t / gran) * gran;
+    if (t < gran) t = gran;
+    if (single_set_when_chunked && md.m > p->wc_cap) t = gran;  // accumulators live across chunks
+    for (long long r0 = 0; r0 < md.n; r0 += t) {
+      const int nr = (int)std::min<long long>(t, md.n - r0);
+      out.push_back(make_int4(i, (int)r0, nr, 0));
+    }
+  }
+}
+
+template <typename T>
+int upload(T** dst, const std::vector<T>& v) {
+  *dst = nullptr;
+  if (v.empty()) return 0;
+  CU(cudaMalloc((void**)dst, v.size() * sizeof(T)));
+  CU(cudaMemcpy(*dst, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+  return 0;
+}
+
+struct PhaseScope {
+  psgd_plan* p;
+  cudaStream_t s;
+  Timer t{};
+  bool on = false;
+  PhaseScope(psgd_plan* plan, int phase, cudaStream_t st) : p(plan), s(st) {
+    if (!p->timing) return;
+    if (!p->free_timers.empty()) {
+      t = p->free_timers.back();
+      p->free_timers.pop_back();
+    } else {
+      if (cudaEventCreate(&t.a) != cudaSuccess || cudaEventCreate(&t.b) != cudaSuccess) return;
+    }
+    t.phase = phase;
+    on = cudaEventRecord(t.a, s) == cudaSuccess;
+  }
+  ~PhaseScope() {
+    if (!on) return;
+    cudaEventRecord(t.b, s);
+    p->timers.push_back(t);
+  }
+};
+
+int check_launch(const char* what) {
+  cudaError_t e = cudaGetLastError();
+  if (e != cudaSuccess) return fail("launch of %s failed: %s", what, cudaGetErrorString(e));
+  g_launches.fetch_add(1, std::memory_order_relaxed);
+  return 0;
+}
+
+int need_device(const psgd_plan* p) {
+  if (!p) return fail("null plan");
+  if (p->device < 0) return fail("plan was created host-only (device < 0): no compute entry point is available");
+  return 0;
+}
+int need_ptrs(const psgd_plan* p) {
+  if (p->cur < 0) return fail("psgd_set_ptrs has not been called on this plan");
+  return 0;
+}
+
+template <typename F>
+int set_smem(F* f, size_t bytes) {
+  if (bytes > 48 * 1024) CU(cudaFuncSetAttribute((const void*)f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+  return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int psgd_abi_version(void) { return PSGD_ABI_VERSION; }
+const char* psgd_last_error(void) { return g_err.c_str(); }
+int64_t psgd_launch_count(void) { return g_launches.load(); }
+
+int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, int n_vec,
+                     const int64_t* vec_len, int device, psgd_plan** out) {
+  if (!out) return fail("out is null");
+  *out = nullptr;
+  if (n_mat < 0 || n_vec < 0) return fail("negative tensor count");
+  if (rank < 1) return fail("rank must be >= 1 (got %d)", rank);
+  if ((n_mat && (!n || !m)) || (n_vec && !vec_len)) return fail("null shape array");
+  psgd_plan* p = new psgd_plan();
+  p->device = device;
+  p->n_mat = n_mat;
+  p->n_vec = n_vec;
+  p->rank = rank;
+
+  int rmax = 1;
+  for (int i = 0; i < n_mat; ++i) {
+    if (n[i] < 0 || m[i] < 0 || n[i] > 0x7fffffffLL || m[i] > 0x7fffffffLL) {
+      delete p;
+      return fail("matrix %d has unsupported shape %lld x %lld", i, (long long)n[i], (long long)m[i]);
+    }
+    const int r = (int)std::min<long long>(std::min<long long>(n[i], m[i]), rank);  // reducer.py:78
+    rmax = std::max(rmax, r);
+  }
+  if (rmax > PSGD_MAX_RANK) {
+    delete p;
+    return fail("effective rank %d exceeds PSGD_MAX_RANK=%d of this build", rmax, PSGD_MAX_RANK);
+  }
+  p->R = pow2_ceil(rmax);
+  const int R = p->R;
+
+  // shared-memory budget of the transposed Q stage -> column chunk width
+  const long long q_stage_bytes = env_ll("PSGD_QSTAGE_BYTES", 96 * 1024);
+  p->wc_cap = (int)std::max<long long>(128, ((q_stage_bytes / 4 / R) / 128) * 128);
+
+  const long long t1_bytes = env_ll("PSGD_T1_BYTES", 128 * 1024);
+  const long long t4_bytes = env_ll("PSGD_T4_BYTES", 96 * 1024);
+  const long long t3_bytes = env_ll("PSGD_T3_BYTES", 128 * 1024);
+  const long long t3_maxblk = env_ll("PSGD_T3_MAXBLK", 48);
+  const int cgw_cap = (int)env_ll("PSGD_T3_CGW", 128);
+
+  p->mats.resize(n_mat);
+  p->q_pre.assign(n_mat + 1, 0);
+  long long po = 0, qo = 0, wo = 0;
+  int mmax = 0;
+  size_t smem3 = 0;
+  for (int i = 0; i < n_mat; ++i) {
+    MatDesc& md = p->mats[i];
+    md.n = (int)n[i];
+    md.m = (int)m[i];
+    md.r = (int)std::min<long long>(std::min<long long>(n[i], m[i]), rank);
+    md.p_off = po;
+    md.q_off = qo;
+    md.ws_off = wo;
+    md.pad_ = 0;
+    po += (long long)md.n * md.r;  // reducer.py:97
+    qo += (long long)md.m * md.r;  // reducer.py:98
+    p->q_pre[i + 1] = qo;
+    mmax = std::max(mmax, md.m);
+
+    // K3 geometry
+    md.cpt = (md.m % 4 == 0 && md.m > 0) ? 4 : 1;
+    const long long groups = std::max<long long>(1, md.m / md.cpt);
+    int cgw = 1;
+    while (cgw * 2 <= cgw_cap && groups % (cgw * 2) == 0) cgw *= 2;
+    if (cgw < 16) cgw = std::min(cgw_cap, pow2_ceil(groups));  // ragged last tile instead of tiny tiles
+    md.cgw = cgw;
+    const long long wbytes = (long long)cgw * md.cpt * 4;
+    long long t3 = std::max<long long>(32, t3_bytes / wbytes);
+    t3 = std::max<long long>(t3, (md.n + t3_maxblk - 1) / t3_maxblk);
+    t3 = std::min<long long>(t3, 2048);
+    t3 = std::min<long long>(t3, std::max(1, md.n));
+    md.t3_rows = (int)t3;
+    md.nblk3 = md.n ? (int)((md.n + t3 - 1) / t3) : 0;
+    wo += (long long)md.nblk3 * md.m * md.r;
+    wo = (wo + 3) & ~3LL;
+    const int RL = kThreads / cgw;
+    const size_t s3 = ((size_t)md.t3_rows * R + (size_t)RL * md.cpt * R * (cgw + 1)) * 4;
+    smem3 = std::max(smem3, s3);
+    const int ncol = (int)((groups + cgw - 1) / cgw);
+    if (md.n && md.m)
+      for (int b = 0; b < md.nblk3; ++b)
+        for (int ct = 0; ct < ncol; ++ct) {
+          ColTile t{};
+          t.mat = i;
+          t.row0 = b * md.t3_rows;
+          t.nrows = std::min(md.t3_rows, md.n - t.row0);
+          t.col0 = ct * cgw * md.cpt;
+          t.blk = b;
+          p->tiles3.push_back(t);
+        }
+  }
+  p->p_total = po;
+  p->q_total = qo;
+  p->ws_total = wo;
+  p->smem3 = smem3;
+
+  const int wc = std::min(std::max(mmax, 1), p->wc_cap);
+  p->smem1 = p->smem4 = (size_t)R * q_pitch(wc, R) * 4;
+
+  const int rows1 = R <= 2 ? 8 : R <= 8 ? 4 : R == 16 ? 2 : 1;
+  const int rows4 = R <= 8 ? 4 : R == 16 ? 2 : 1;
+  build_row_tiles(p, p->tiles1, t1_bytes, rows1, true);
+  build_row_tiles(p, p->tiles4, t4_bytes, rows4, false);
+
+  p->v_pre.assign(n_vec + 1, 0);
+  for (int j = 0; j < n_vec; ++j) {
+    if (vec_len[j] < 0) {
+      delete p;
+      return fail("vector %d has negative length", j);
+    }
+    p->v_pre[j + 1] = p->v_pre[j] + vec_len[j];  // tensor_buffer.py:11-13
+  }
+  p->v_total = p->v_pre[n_vec];
+
+  if (device >= 0) {
+    int rc = 0;
+    cudaError_t e = cudaSetDevice(device);
+    if (e != cudaSuccess) {
+      delete p;
+      return fail("cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
+    }
+    rc |= upload(&p->d_mats, p->mats);
+    rc |= upload(&p->d_tiles1, p->tiles1);
+    rc |= upload(&p->d_tiles4, p->tiles4);
+    rc |= upload(&p->d_tiles3, p->tiles3);
+    rc |= upload(&p->d_q_pre, p->q_pre);
+    rc |= upload(&p->d_v_pre, p->v_pre);
+    // ring slot: 5 pointer arrays + flags per matrix, 2 pointer arrays per vector
+    size_t sb = (size_t)n_mat * (5 * sizeof(void*) + sizeof(unsigned)) + (size_t)n_vec * 2 * sizeof(void*);
+    sb = (sb + 255) & ~(size_t)255;
+    if (sb == 0) sb = 256;
+    p->slot_bytes = sb;
+    if (!rc && cudaMallocHost((void**)&p->h_ring, sb * kSlots) != cudaSuccess) rc = fail("cudaMallocHost failed");
+    if (!rc && cudaMalloc((void**)&p->d_ring, sb * kSlots) != cudaSuccess) rc = fail("cudaMalloc(ring) failed");
+    for (int s = 0; s < kSlots && !rc; ++s)
+      if (cudaEventCreateWithFlags(&p->slot_ev[s], cudaEventDisableTiming) != cudaSuccess) rc = fail("cudaEventCreate failed");
+    if (rc) {
+      std::string keep = g_err;
+      psgd_plan_destroy(p);
+      g_err = keep;
+      return 1;
+    }
+  }
+  *out = p;
+  return 0;
+}
+
+int psgd_plan_destroy(psgd_plan* p) {
+  if (!p) return 0;
+  if (p->device >= 0) {
+    cudaSetDevice(p->device);
+    cudaFree(p->d_mats);
+    cudaFree(p->d_tiles1);
+    cudaFree(p->d_tiles4);
+    cudaFree(p->d_tiles3);
+    cudaFree(p->d_q_pre);
+    cudaFree(p->d_v_pre);
+    cudaFree(p->d_ring);
+    if (p->h_ring) cudaFreeHost(p->h_ring);
+    for (int s = 0; s < kSlots; ++s)
+      if (p->slot_ev[s]) cudaEventDestroy(p->slot_ev[s]);
+    for (auto& t : p->timers) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
+    for (auto& t : p->free_timers) { cudaEventDestroy(t.a); cudaEventDestroy(t.b); }
+  }
+  delete p;
+  return 0;
+}
+
+int64_t psgd_p_elems(const psgd_plan* p) { return p ? p->p_total : -1; }
+int64_t psgd_q_elems(const psgd_plan* p) { return p ? p->q_total : -1; }
+int64_t psgd_vec_elems(const psgd_plan* p) { return p ? p->v_total : -1; }
+int64_t psgd_workspace_bytes(const psgd_plan* p) { return p ? std::max<long long>(16, p->ws_total * 4) : -1; }
+
+int psgd_matrix_info(const psgd_plan* p, int i, int64_t* o) {
+  if (!p || !o || i < 0 || i >= p->n_mat) return fail("psgd_matrix_info: bad argument");
+  const MatDesc& md = p->mats[i];
+  o[0] = md.n; o[1] = md.m; o[2] = md.r; o[3] = md.p_off; o[4] = md.q_off; o[5] = md.ws_off;
+  o[6] = md.nblk3; o[7] = (int64_t)md.cgw * md.cpt;
+  return 0;
+}
+
+int psgd_tile_count(const psgd_plan* p, int phase) {
+  if (!p) return -1;
+  switch (phase) {
+    case PSGD_PHASE_P_FROM_M: return (int)p->tiles1.size();
+    case PSGD_PHASE_FINALIZE: return (int)p->tiles4.size();
+    case PSGD_PHASE_Q_FROM_MT: return (int)p->tiles3.size();
+    case PSGD_PHASE_ORTH: return p->n_mat * kOrthCluster;
+    default: return 0;
+  }
+}
+
+int psgd_tile_get(const psgd_plan* p, int phase, int idx, int32_t* o) {
+  if (!p || !o || idx < 0 || idx >= psgd_tile_count(p, phase)) return fail("psgd_tile_get: bad argument");
+  if (phase == PSGD_PHASE_P_FROM_M || phase == PSGD_PHASE_FINALIZE) {
+    const int4 t = (phase == PSGD_PHASE_P_FROM_M ? p->tiles1 : p->tiles4)[idx];
+    o[0] = t.x; o[1] = t.y; o[2] = t.z; o[3] = 0; o[4] = p->mats[t.x].m; o[5] = 0;
+  } else if (phase == PSGD_PHASE_Q_FROM_MT) {
+    const ColTile& t = p->tiles3[idx];
+    const MatDesc& md = p->mats[t.mat];
+    o[0] = t.mat; o[1] = t.row0; o[2] = t.nrows; o[3] = t.col0;
+    o[4] = std::min(md.cgw * md.cpt, md.m - t.col0); o[5] = t.blk;
+  } else {
+    return fail("psgd_tile_get: phase %d has no tile table", phase);
+  }
+  return 0;
+}
+
+int psgd_set_ptrs(psgd_plan* p, const void* const* mat_in, void* const* mat_out, void* const* mat_mem,
+                  const void* const* vec_in, void* const* vec_out, const void* const* grad,
+                  const void* const* err, psgd_stream stream) {
+  if (need_device(p)) return 1;
+  if (p->n_mat && (!mat_in || !mat_out || !mat_mem)) return fail("psgd_set_ptrs: null matrix pointer array");
+  if (p->n_vec && (!vec_in || !vec_out)) return fail("psgd_set_ptrs: null vector pointer array");
+  CU(cudaSetDevice(p->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  const int slot = (p->cur + 1) % kSlots;
+  if (p->slot_used[slot]) CU(cudaEventSynchronize(p->slot_ev[slot]));  // its upload has left the host buffer
+  char* h = p->h_ring + (size_t)slot * p->slot_bytes;
+  char* d = p->d_ring + (size_t)slot * p->slot_bytes;
+  const size_t L = p->n_mat, L1 = p->n_vec;
+  const void** h_in = (const void**)h;
+  void** h_out = (void**)(h + L * 8);
+  void** h_mem = (void**)(h + 2 * L * 8);
+  const void** h_g = (const void**)(h + 3 * L * 8);
+  const void** h_e = (const void**)(h + 4 * L * 8);
+  const void** h_vin = (const void**)(h + 5 * L * 8);
+  void** h_vout = (void**)(h + 5 * L * 8 + L1 * 8);
+  unsigned* h_fl = (unsigned*)(h + 5 * L * 8 + 2 * L1 * 8);
+  p->have_ge = grad && err;
+  for (size_t i = 0; i < L; ++i) {
+    const MatDesc& md = p->mats[i];
+    const bool nonempty = md.n && md.m;
+    if (nonempty && (!mat_in[i] || !mat_out[i] || !mat_mem[i])) return fail("psgd_set_ptrs: matrix %zu has a null pointer", i);
+    if (((uintptr_t)mat_in[i] | (uintptr_t)mat_out[i] | (uintptr_t)mat_mem[i]) & 3)
+      return fail("psgd_set_ptrs: matrix %zu is not 4-byte aligned", i);
+    h_in[i] = mat_in[i];
+    h_out[i] = mat_out[i];
+    h_mem[i] = mat_mem[i];
+    h_g[i] = p->have_ge ? grad[i] : nullptr;
+    h_e[i] = p->have_ge ? err[i] : nullptr;
+    unsigned fl = 0;
+    const bool m4 = md.m % 4 == 0;
+    if (m4 && ((uintptr_t)mat_in[i] & 15) == 0) fl |= kFlagInVec;
+    if (m4 && (((uintptr_t)mat_out[i] | (uintptr_t)mat_mem[i]) & 15) == 0) fl |= kFlagOutVec;
+    if (p->have_ge && m4 && (((uintptr_t)grad[i] | (uintptr_t)err[i]) & 15) == 0) fl |= kFlagGeVec;
+    h_fl[i] = fl;
+  }
+  for (size_t j = 0; j < L1; ++j) {
+    const bool nonempty = p->v_pre[j + 1] > p->v_pre[j];
+    if (nonempty && (!vec_in[j] || !vec_out[j])) return fail("psgd_set_ptrs: vector %zu has a null pointer", j);
+    h_vin[j] = vec_in[j];
+    h_vout[j] = vec_out[j];
+  }
+  CU(cudaMemcpyAsync(d, h, p->slot_bytes, cudaMemcpyHostToDevice, s));
+  CU(cudaEventRecord(p->slot_ev[slot], s));
+  p->slot_used[slot] = true;
+  p->cur = slot;
+  p->slot.in = (const float* const*)d;
+  p->slot.out = (float* const*)(d + L * 8);
+  p->slot.mem = (float* const*)(d + 2 * L * 8);
+  p->slot.g = (const float* const*)(d + 3 * L * 8);
+  p->slot.e = (const float* const*)(d + 4 * L * 8);
+  p->slot.vin = (const float* const*)(d + 5 * L * 8);
+  p->slot.vout = (float* const*)(d + 5 * L * 8 + L1 * 8);
+  p->slot.flags = (const unsigned*)(d + 5 * L * 8 + 2 * L1 * 8);
+  return 0;
+}
+
+int psgd_pack_vec(psgd_plan* p, float* flat, psgd_stream stream) {
+  if (need_device(p) || need_ptrs(p)) return 1;
+  if (p->v_total == 0) return 0;
+  if (!flat) return fail("psgd_pack_vec: flat is null");
+  CU(cudaSetDevice(p->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  PhaseScope ts(p, PSGD_PHASE_PACK, s);
+  const unsigned grid = (unsigned)((p->v_total + kThreads - 1) / kThreads);
+  k_gather<uint32_t><<<grid, kThreads, 0, s>>>(p->d_v_pre, p->n_vec, (const void* const*)p->slot.vin,
+                                                (uint32_t*)flat, p->v_total);
+  return check_launch("k_gather");
+}
+
+#define DISPATCH_R(R_, ...)                    \
+  switch (R_) {                                \
+    case 1: { constexpr int RR = 1; __VA_ARGS__; } break;   \
+    case 2: { constexpr int RR = 2; __VA_ARGS__; } break;   \
+    case 4: { constexpr int RR = 4; __VA_ARGS__; } break;   \
+    case 8: { constexpr int RR = 8; __VA_ARGS__; } break;   \
+    case 16: { constexpr int RR = 16; __VA_ARGS__; } break; \
+    case 32: { constexpr int RR = 32; __VA_ARGS__; } break; \
+    default: return fail("unsupported compile-time rank %d", R_); \
+  }
+
+int psgd_p_from_m(psgd_plan* p, float* p_mem, const float* q_mem, int fuse_add, float q_div, psgd_stream stream) {
+  if (need_device(p) || need_ptrs(p)) return 1;
+  if (p->tiles1.empty()) return 0;
+  if (!p_mem || !q_mem) return fail("psgd_p_from_m: null p_mem/q_mem");
+  if (fuse_add && !p->have_ge) return fail("psgd_p_from_m: fuse_add needs grad/err pointers in psgd_set_ptrs");
+  if (!(q_div > 0.f)) return fail("psgd_p_from_m: q_div must be positive");
+  CU(cudaSetDevice(p->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  const DevPlan dp = dev_plan(p);
+  const unsigned grid = (unsigned)p->tiles1.size();
+  PhaseScope ts(p, PSGD_PHASE_P_FROM_M, s);
+  DISPATCH_R(p->R, {
+    if (fuse_add) {
+      if (set_smem(k_p_from_m<RR, true>, p->smem1)) return 1;
+      k_p_from_m<RR, true><<<grid, kThreads, p->smem1, s>>>(dp, p->slot, q_mem, p_mem, q_div);
+    } else {
+      if (set_smem(k_p_from_m<RR, false>, p->smem1)) return 1;
+      k_p_from_m<RR, false><<<grid, kThreads, p->smem1, s>>>(dp, p->slot, q_mem, p_mem, q_div);
+    }
+  });
+  return check_launch("k_p_from_m");
+}
+
+int psgd_orthogonalize(psgd_plan* p, float* p_mem, float n_workers, psgd_stream stream) {
+  if (need_device(p)) return 1;
+  if (p->n_mat == 0) return 0;
+  if (!p_mem) return fail("psgd_orthogonalize: null p_mem");
+  if (!(n_workers >= 1.f)) return fail("psgd_orthogonalize: n_workers must be >= 1");
+  CU(cudaSetDevice(p->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  const DevPlan dp = dev_plan(p);
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3((unsigned)p->n_mat * kOrthCluster);
+  cfg.blockDim = dim3(kOrthThreads);
+  cfg.dynamicSmemBytes = 0;
+  cfg.stream = s;
+  cudaLaunchAttribute at[1];
+  at[0].id = cudaLaunchAttributeClusterDimension;
+  at[0].val.clusterDim.x = kOrthCluster;
+  at[0].val.clusterDim.y = 1;
+  at[0].val.clusterDim.z = 1;
+  cfg.attrs = at;
+  cfg.numAttrs = 1;
+  PhaseScope ts(p, PSGD_PHASE_ORTH, s);
+  DISPATCH_R(p->R, { CU(cudaLaunchKernelEx(&cfg, k_orthogonalize<RR>, dp, p_mem, n_workers)); });
+  return check_launch("k_orthogonalize");
+}
+
+int psgd_q_from_mt(psgd_plan* p, const float* p_mem, float* q_mem, void* workspace, psgd_stream stream) {
+  if (need_device(p) || need_ptrs(p)) return 1;
+  if (p->tiles3.empty()) return 0;
+  if (!p_mem || !q_mem || !workspace) return fail("psgd_q_from_mt: null p_mem/q_mem/workspace");
+  if ((uintptr_t)workspace & 15) return fail("psgd_q_from_mt: workspace must be 16-byte aligned");
+  CU(cudaSetDevice(p->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  const DevPlan dp = dev_plan(p);
+  float* ws = (float*)workspace;
+  {
+    PhaseScope ts(p, PSGD_PHASE_Q_FROM_MT, s);
+    const unsigned grid = (unsigned)p->tiles3.size();
+    DISPATCH_R(p->R, {
+      if (set_smem(k_q_from_mt<RR>, p->smem3)) return 1;
+      k_q_from_mt<RR><<<grid, kThreads, p->smem3, s>>>(dp, p->slot, p_mem, ws);
+    });
+    if (check_launch("k_q_from_mt")) return 1;
+  }
+  {
+    PhaseScope ts(p, PSGD_PHASE_Q_REDUCE, s);
+    const unsigned grid = (unsigned)((p->q_total + kThreads - 1) / kThreads);
+    k_q_reduce<<<grid, kThreads, 0, s>>>(dp, ws, q_mem, p->q_total);
+    if (check_launch("k_q_reduce")) return 1;
+  }
+  return 0;
+}
+
+int psgd_finalize(psgd_plan* p, const float* p_mem, const float* q_mem, float n_workers, psgd_stream stream) {
+  if (need_device(p) || need_ptrs(p)) return 1;
+  if (p->tiles4.empty()) return 0;
+  if (!p_mem || !q_mem) return fail("psgd_finalize: null p_mem/q_mem");
+  if (!(n_workers >= 1.f)) return fail("psgd_finalize: n_workers must be >= 1");
+  CU(cudaSetDevice(p->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  const DevPlan dp = dev_plan(p);
+  const unsigned grid = (unsigned)p->tiles4.size();
+  PhaseScope ts(p, PSGD_PHASE_FINALIZE, s);
+  DISPATCH_R(p->R, {
+    if (set_smem(k_finalize<RR>, p->smem4)) return 1;
+    k_finalize<RR><<<grid, kThreads, p->smem4, s>>>(dp, p->slot, p_mem, q_mem, n_workers);
+  });
+  return check_launch("k_finalize");
+}
+
+int psgd_finish(psgd_plan* p, const float* flat, float* q_mem, float n_workers, psgd_stream stream) {
+  if (need_device(p) || need_ptrs(p)) return 1;
+  if (!(n_workers >= 1.f)) return fail("psgd_finish: n_workers must be >= 1");
+  const long long qn = q_mem ? p->q_total : 0;
+  const long long total = p->v_total + qn;
+  if (total == 0) return 0;
+  if (p->v_total && !flat) return fail("psgd_finish: flat is null");
+  CU(cudaSetDevice(p->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  PhaseScope ts(p, PSGD_PHASE_FINISH, s);
+  const unsigned grid = (unsigned)((total + kThreads - 1) / kThreads);
+  k_finish<<<grid, kThreads, 0, s>>>(dev_plan(p), p->slot, flat, p->v_total, q_mem, qn, n_workers);
+  return check_launch("k_finish");
+}
+
+int psgd_timing_enable(psgd_plan* p, int on) {
+  if (need_device(p)) return 1;
+  p->timing = on != 0;
+  return 0;
+}
+
+int psgd_timing_read(psgd_plan* p, double* ms_sum, int64_t* count) {
+  if (need_device(p)) return 1;
+  CU(cudaSetDevice(p->device));
+  for (auto& t : p->timers) {
+    CU(cudaEventSynchronize(t.b));
+    float ms = 0.f;
+    CU(cudaEventElapsedTime(&ms, t.a, t.b));
+    p->ms_sum[t.phase] += ms;
+    p->ms_cnt[t.phase] += 1;
+    p->free_timers.push_back(t);
+  }
+  p->timers.clear();
+  for (int i = 0; i < PSGD_N_PHASES; ++i) {
+    if (ms_sum) ms_sum[i] = p->ms_sum[i];
+    if (count) count[i] = p->ms_cnt[i];
+    p->ms_sum[i] = 0;
+    p->ms_cnt[i] = 0;
+  }
+  return 0;
+}
+
+// ---- stand-alone TensorBuffer packer -----------------------------------------------------
+
+int psgd_tb_create(int n, const int64_t* nelem, int elem_size, int device, psgd_tb** out) {
+  if (!out) return fail("out is null");
+  *out = nullptr;
+  if (n < 0 || (n && !nelem)) return fail("psgd_tb_create: bad tensor list");
+  if (elem_size != 1 && elem_size != 2 && elem_size != 4 && elem_size != 8)
+    return fail("psgd_tb_create: element size %d not supported (1, 2, 4, 8)", elem_size);
+  if (device < 0) return fail("psgd_tb_create: needs a CUDA device");
+  psgd_tb* tb = new psgd_tb();
+  tb->device = device;
+  tb->n = n;
+  tb->elem_size = elem_size;
+  tb->pre.assign(n + 1, 0);
+  for (int i = 0; i < n; ++i) {
+    if (nelem[i] < 0) { delete tb; return fail("psgd_tb_create: negative length"); }
+    tb->pre[i + 1] = tb->pre[i] + nelem[i];
+  }
+  tb->total = tb->pre[n];
+  tb->slot_bytes = std::max<size_t>(256, ((size_t)n * 8 + 255) & ~(size_t)255);
+  int rc = 0;
+  if (cudaSetDevice(device) != cudaSuccess) rc = fail("cudaSetDevice(%d) failed", device);
+  if (!rc) rc = upload(&tb->d_pre, tb->pre);
+  if (!rc && cudaMallocHost((void**)&tb->h_ring, tb->slot_bytes * kSlots) != cudaSuccess) rc = fail("cudaMallocHost failed");
+  if (!rc && cudaMalloc((void**)&tb->d_ring, tb->slot_bytes * kSlots) != cudaSuccess) rc = fail("cudaMalloc failed");
+  for (int s = 0; s < kSlots && !rc; ++s)
+    if (cudaEventCreateWithFlags(&tb->slot_ev[s], cudaEventDisableTiming) != cudaSuccess) rc = fail("cudaEventCreate failed");
+  if (rc) {
+    std::string keep = g_err;
+    psgd_tb_destroy(tb);
+    g_err = keep;
+    return 1;
+  }
+  *out = tb;
+  return 0;
+}
+
+int psgd_tb_destroy(psgd_tb* tb) {
+  if (!tb) return 0;
+  cudaSetDevice(tb->device);
+  cudaFree(tb->d_pre);
+  cudaFree(tb->d_ring);
+  if (tb->h_ring) cudaFreeHost(tb->h_ring);
+  for (int s = 0; s < kSlots; ++s)
+    if (tb->slot_ev[s]) cudaEventDestroy(tb->slot_ev[s]);
+  delete tb;
+  return 0;
+}
+
+static int tb_upload(psgd_tb* tb, const void* const* ptrs, cudaStream_t s, void*** d_out) {
+  const int slot = tb->cur;
+  tb->cur = (tb->cur + 1) % kSlots;
+  if (tb->slot_used[slot]) CU(cudaEventSynchronize(tb->slot_ev[slot]));
+  char* h = tb->h_ring + (size_t)slot * tb->slot_bytes;
+  char* d = tb->d_ring + (size_t)slot * tb->slot_bytes;
+  for (int i = 0; i < tb->n; ++i) {
+    if (!ptrs[i] && tb->pre[i + 1] > tb->pre[i]) return fail("tensor %d has a null pointer", i);
+    if ((uintptr_t)ptrs[i] % tb->elem_size) return fail("tensor %d is not aligned to its element size", i);
+    ((const void**)h)[i] = ptrs[i];
+  }
+  CU(cudaMemcpyAsync(d, h, (size_t)tb->n * 8, cudaMemcpyHostToDevice, s));
+  CU(cudaEventRecord(tb->slot_ev[slot], s));
+  tb->slot_used[slot] = true;
+  *d_out = (void**)d;
+  return 0;
+}
+
+int psgd_tb_pack(psgd_tb* tb, const void* const* src, void* flat, psgd_stream stream) {
+  if (!tb) return fail("null tensor buffer");
+  if (tb->total == 0) return 0;
+  if (!src || !flat) return fail("psgd_tb_pack: null argument");
+  CU(cudaSetDevice(tb->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  void** d = nullptr;
+  if (tb_upload(tb, src, s, &d)) return 1;
+  const unsigned grid = (unsigned)((tb->total + kThreads - 1) / kThreads);
+  switch (tb->elem_size) {
+    case 1: k_gather<uint8_t><<<grid, kThreads, 0, s>>>(tb->d_pre, tb->n, (const void* const*)d, (uint8_t*)flat, tb->total); break;
+    case 2: k_gather<uint16_t><<<grid, kThreads, 0, s>>>(tb->d_pre, tb->n, (const void* const*)d, (uint16_t*)flat, tb->total); break;
+    case 4: k_gather<uint32_t><<<grid, kThreads, 0, s>>>(tb->d_pre, tb->n, (const void* const*)d, (uint32_t*)flat, tb->total); break;
+    default: k_gather<uint64_t><<<grid, kThreads, 0, s>>>(tb->d_pre, tb->n, (const void* const*)d, (uint64_t*)flat, tb->total); break;
+  }
+  return check_launch("k_gather");
+}
+
+int psgd_tb_unpack(psgd_tb* tb, const void* flat, void* const* dst, psgd_stream stream) {
+  if (!tb) return fail("null tensor buffer");
+  if (tb->total == 0) return 0;
+  if (!dst || !flat) return fail("psgd_tb_unpack: null argument");
+  CU(cudaSetDevice(tb->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  void** d = nullptr;
+  if (tb_upload(tb, (const void* const*)dst, s, &d)) return 1;
+  const unsigned grid = (unsigned)((tb->total + kThreads - 1) / kThreads);
+  switch (tb->elem_size) {
+    case 1: k_scatter<uint8_t><<<grid, kThreads, 0, s>>>(tb->d_pre, tb->n, (const uint8_t*)flat, (void* const*)d, tb->total); break;
+    case 2: k_scatter<uint16_t><<<grid, kThreads, 0, s>>>(tb->d_pre, tb->n, (const uint16_t*)flat, (void* const*)d, tb->total); break;
+    case 4: k_scatter<uint32_t><<<grid, kThreads, 0, s>>>(tb->d_pre, tb->n, (const uint32_t*)flat, (void* const*)d, tb->total); break;
+    default: k_scatter<uint64_t><<<grid, kThreads, 0, s>>>(tb->d_pre, tb->n, (const uint64_t*)flat, (void* const*)d, tb->total); break;
+  }
+  return check_launch("k_scatter");
+}
+
+int psgd_orthogonalize_one(float* mat, int64_t n, int r, int device, psgd_stream stream) {
+  if (n < 0 || r < 0) return fail("psgd_orthogonalize_one: negative shape");
+  if (n == 0 || r == 0) return 0;
+  if (!mat) return fail("psgd_orthogonalize_one: null matrix");
+  if (r > PSGD_MAX_RANK) return fail("psgd_orthogonalize_one: %d columns exceed PSGD_MAX_RANK=%d", r, PSGD_MAX_RANK);
+  if (n > 0x7fffffffLL) return fail("psgd_orthogonalize_one: too many rows");
+  CU(cudaSetDevice(device));
+  cudaStream_t s = (cudaStream_t)stream;
+  const int R = pow2_ceil(r);
+  DISPATCH_R(R, { k_orthogonalize_one<RR><<<1, kOrthThreads, 0, s>>>(mat, (int)n, r); });
+  return check_launch("k_orthogonalize_one");
+}
+
+}  // extern "C"

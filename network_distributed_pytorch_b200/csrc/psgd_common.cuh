@@ -1,0 +1,214 @@
+// Shared device-side types and small helpers for the PowerSGD kernels (sm_100a).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace psgd {
+
+constexpr int kThreads = 256;      // CTA size of the streaming kernels (8 warps)
+constexpr int kWarps = kThreads / 32;
+constexpr int kOrthThreads = 512;  // CTA size of the Gram-Schmidt kernel
+constexpr int kOrthCluster = 8;    // CTAs per matrix (one thread-block cluster)
+
+// per-matrix constants, uploaded once per plan
+struct MatDesc {
+  long long p_off;   // element offset of P_i in p_mem   (reducer.py:95)
+  long long q_off;   // element offset of Q_i in q_mem   (reducer.py:96)
+  long long ws_off;  // element offset of the K3 partials of this matrix in the workspace
+  int n, m, r;       // rows, columns, r = min(n, m, rank) (reducer.py:76-78)
+  int cgw;           // K3: column groups (threads) per tile row, power of two <= kThreads
+  int cpt;           // K3: columns per thread (4 when m % 4 == 0, else 1)
+  int t3_rows;       // K3: rows per tile
+  int nblk3;         // K3: row blocks = ceil(n / t3_rows)
+  int pad_;
+};
+static_assert(sizeof(MatDesc) == 56, "MatDesc layout");
+
+// K3 tile: matrix, first row, row count, first column, row-block index
+struct ColTile {
+  int mat, row0, nrows, col0;
+  int blk, pad0, pad1, pad2;
+};
+
+// device views of the per-step pointer arrays (one ring slot)
+struct PtrSlot {
+  const float* const* in;   // M_i   (grad_in,  reducer.py:43)
+  float* const* out;        // grad_out
+  float* const* mem;        // memory_out
+  const float* const* g;    // raw gradient  (fuse_add)
+  const float* const* e;    // error memory  (fuse_add)
+  const unsigned* flags;    // alignment flags per matrix
+  const float* const* vin;  // <=1-D inputs
+  float* const* vout;       // <=1-D outputs
+};
+
+enum : unsigned {
+  kFlagInVec = 1u,   // M_i 16-byte aligned and m % 4 == 0
+  kFlagOutVec = 2u,  // out_i and mem_i 16-byte aligned
+  kFlagGeVec = 4u,   // grad_i and err_i 16-byte aligned
+};
+
+struct DevPlan {
+  const MatDesc* mats;
+  const int4* tiles1;      // K1 row tiles {mat, row0, nrows, -}
+  const int4* tiles4;      // K4 row tiles
+  const ColTile* tiles3;   // K3 tiles
+  const long long* q_pre;  // n_mat + 1 prefix of q offsets
+  const long long* v_pre;  // n_vec + 1 prefix of vector offsets
+  int n_mat, n_vec;
+  int wc_cap;              // max columns of Q staged in shared memory at once
+  int pad_;
+};
+
+// ---- memory helpers -------------------------------------------------------------------
+
+// streaming 128-bit load: read-only path, do not allocate in L1 (M is touched once per pass)
+__device__ __forceinline__ float4 ld_stream4(const float* p) {
+  float4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w)
+               : "l"(p));
+  return v;
+}
+__device__ __forceinline__ float ld_stream1(const float* p) {
+  float v;
+  asm volatile("ld.global.nc.L1::no_allocate.f32 %0, [%1];" : "=f"(v) : "l"(p));
+  return v;
+}
+__device__ __forceinline__ void st_stream4(float* p, float4 v) {
+  asm volatile("st.global.L1::no_allocate.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(p), "f"(v.x), "f"(v.y),
+               "f"(v.z), "f"(v.w)
+               : "memory");
+}
+__device__ __forceinline__ void st_stream1(float* p, float v) {
+  asm volatile("st.global.L1::no_allocate.f32 [%0], %1;" ::"l"(p), "f"(v) : "memory");
+}
+
+// V consecutive floats; V = 4 uses 128-bit accesses, V = 1 is the unaligned fallback
+template <int V>
+struct Pack {
+  float v[V];
+};
+template <int V>
+__device__ __forceinline__ Pack<V> pk_zero() {
+  Pack<V> r;
+#pragma unroll
+  for (int i = 0; i < V; ++i) r.v[i] = 0.f;
+  return r;
+}
+template <int V>
+__device__ __forceinline__ Pack<V> pk_ld_stream(const float* p);
+template <>
+__device__ __forceinline__ Pack<4> pk_ld_stream<4>(const float* p) {
+  float4 t = ld_stream4(p);
+  Pack<4> r;
+  r.v[0] = t.x; r.v[1] = t.y; r.v[2] = t.z; r.v[3] = t.w;
+  return r;
+}
+template <>
+__device__ __forceinline__ Pack<1> pk_ld_stream<1>(const float* p) {
+  Pack<1> r;
+  r.v[0] = ld_stream1(p);
+  return r;
+}
+template <int V>
+__device__ __forceinline__ void pk_st_stream(float* p, const Pack<V>& a);
+template <>
+__device__ __forceinline__ void pk_st_stream<4>(float* p, const Pack<4>& a) {
+  st_stream4(p, make_float4(a.v[0], a.v[1], a.v[2], a.v[3]));
+}
+template <>
+__device__ __forceinline__ void pk_st_stream<1>(float* p, const Pack<1>& a) {
+  st_stream1(p, a.v[0]);
+}
+template <int V>
+__device__ __forceinline__ Pack<V> pk_ld_shared(const float* p);
+template <>
+__device__ __forceinline__ Pack<4> pk_ld_shared<4>(const float* p) {
+  float4 t = *reinterpret_cast<const float4*>(p);
+  Pack<4> r;
+  r.v[0] = t.x; r.v[1] = t.y; r.v[2] = t.z; r.v[3] = t.w;
+  return r;
+}
+template <>
+__device__ __forceinline__ Pack<1> pk_ld_shared<1>(const float* p) {
+  Pack<1> r;
+  r.v[0] = *p;
+  return r;
+}
+
+// Shared-memory row pitch (floats) of the transposed Q stage: multiple of 4 (128-bit reads)
+// and skewed so the transposing stores of `R` interleaved columns spread over the banks.
+__host__ __device__ inline int q_pitch(int wc, int R) {
+  int skew = 32 / R;
+  if (skew < 4) skew = 4;
+  if (R == 1) skew = 0;
+  return ((wc + 31) / 32) * 32 + skew;
+}
+
+// Stage columns [c0, c0+wc) of the row-major m x r matrix Q into shared memory transposed:
+// Qs[c * pitch + j] = Q[(c0 + j) * r + c] / div ; rows c in [r, R) are zero filled so the
+// compute loops can run with the compile-time rank R.
+template <int R>
+__device__ __forceinline__ void stage_q(float* Qs, const float* __restrict__ Q, int c0, int wc,
+                                        int r, int pitch, float div) {
+  const float* src = Q + (size_t)c0 * r;
+  const int total = wc * r;
+  for (int e = threadIdx.x; e < total; e += blockDim.x) {
+    const int j = e / r;
+    const int c = e - j * r;
+    float v = __ldg(src + e);
+    if (div != 1.0f) v = v / div;
+    Qs[c * pitch + j] = v;
+  }
+  if (r < R) {
+    const int zt = (R - r) * wc;
+    for (int e = threadIdx.x; e < zt; e += blockDim.x) {
+      const int c = r + e / wc;
+      const int j = e % wc;
+      Qs[c * pitch + j] = 0.f;
+    }
+  }
+}
+
+// Butterfly "transpose-reduce": every lane enters with NV partial sums; on return lane L
+// holds in v[0] the sum over all 32 lanes of partial number (L / (32 / NV)).  NV-1 shuffles
+// for the folding steps plus log2(32/NV) plain steps instead of 5 * NV.
+template <int NV>
+__device__ __forceinline__ float warp_fold(float (&v)[NV], int lane) {
+  static_assert(NV == 1 || NV == 2 || NV == 4 || NV == 8 || NV == 16 || NV == 32, "NV");
+  int bit = 16;
+#pragma unroll
+  for (int half = NV / 2; half >= 1; half /= 2) {
+    const bool upper = (lane & bit) != 0;
+#pragma unroll
+    for (int i = 0; i < half; ++i) {
+      const float send = upper ? v[i] : v[i + half];
+      const float keep = upper ? v[i + half] : v[i];
+      v[i] = keep + __shfl_xor_sync(0xffffffffu, send, bit);
+    }
+    bit >>= 1;
+  }
+  float x = v[0];
+#pragma unroll
+  for (; bit >= 1; bit >>= 1) x += __shfl_xor_sync(0xffffffffu, x, bit);
+  return x;
+}
+
+__device__ __forceinline__ float warp_sum(float x) {
+#pragma unroll
+  for (int o = 16; o >= 1; o >>= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+  return x;
+}
+
+// index of the last prefix entry <= x  (pre has n + 1 entries, pre[0] = 0)
+__device__ __forceinline__ int find_segment(const long long* __restrict__ pre, int n, long long x) {
+  int lo = 0, hi = n;  // answer in [lo, hi)
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (__ldg(pre + mid) <= x) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+}  // namespace psgd

@@ -1,0 +1,567 @@
+// Hand-written sm_100a kernels of the PowerSGD reducer hot path.
+//
+// One launch per phase over a device-side table of all gradient matrices ("grouped
+// launch"): blockIdx.x selects a tile, the tile names its matrix.  All contractions have
+// rank r <= 32 and are HBM-bound, so the kernels are plain FFMA streaming kernels:
+// 128-bit coalesced loads of M, Q staged (transposed) in shared memory, warp-shuffle
+// reductions.  Citations are to ddp_powersgd_guide_cifar10/reducer.py upstream.
+#pragma once
+#include <cooperative_groups.h>
+
+#include "psgd_common.cuh"
+
+namespace psgd {
+namespace cg = cooperative_groups;
+
+// rows a warp carries at once in K1 / K4 for compile-time rank R
+template <int R> struct RowsK1 { static constexpr int v = (R <= 2) ? 8 : (R <= 8) ? 4 : (R == 16) ? 2 : 1; };
+template <int R> struct RowsK4 { static constexpr int v = (R <= 8) ? 4 : (R == 16) ? 2 : 1; };
+
+// =======================================================================================
+// K1:  P = M Q   (reducer.py:121-123), optionally M = grad + err first (ddp_init.py:155-157)
+// Tile = `nrows` full rows of one matrix (a contiguous span of M).  Each warp carries ROWS
+// rows at a time; lanes stride over the columns in 128-bit steps, so a warp reads 512
+// contiguous bytes per row per step.  Q values come from the transposed shared copy and
+// are reused for the ROWS rows.  Partial sums are folded across the warp with shuffles.
+// =======================================================================================
+template <int R, int ROWS, int V, bool FUSE>
+__device__ __forceinline__ void p_tile(const MatDesc& md, const float* __restrict__ M,
+                                       const float* __restrict__ G, const float* __restrict__ E,
+                                       float* __restrict__ Mw, const float* __restrict__ Q,
+                                       float* __restrict__ P, int row0, int nrows, int wc_cap,
+                                       float q_div, float* Qs) {
+  constexpr int NV = R * ROWS;
+  const int m = md.m, r = md.r;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nsets = (nrows + ROWS - 1) / ROWS;
+  const int nchunks = (m + wc_cap - 1) / wc_cap;
+  const int pitch = q_pitch(m < wc_cap ? m : wc_cap, R);
+
+  for (int sb = 0; sb < nsets; sb += kWarps) {
+    const int set = sb + warp;
+    const bool live = set < nsets;
+    const int rbase = set * ROWS;  // tile-relative
+    float acc[ROWS][R];
+#pragma unroll
+    for (int a = 0; a < ROWS; ++a)
+#pragma unroll
+      for (int c = 0; c < R; ++c) acc[a][c] = 0.f;
+
+    for (int ch = 0; ch < nchunks; ++ch) {
+      const int c0 = ch * wc_cap;
+      const int wc = (m - c0 < wc_cap) ? (m - c0) : wc_cap;
+      if (nchunks > 1 || sb == 0) {  // block-uniform: restage only when the chunk changes
+        if (!(ch == 0 && sb == 0)) __syncthreads();
+        stage_q<R>(Qs, Q, c0, wc, r, pitch, q_div);
+        __syncthreads();
+      }
+      if (!live) continue;
+
+      size_t roff[ROWS];
+#pragma unroll
+      for (int a = 0; a < ROWS; ++a) {
+        int rr = rbase + a;
+        if (rr > nrows - 1) rr = nrows - 1;  // clamp: loads stay in bounds, result discarded
+        roff[a] = (size_t)(row0 + rr) * m + c0;
+      }
+      const int kmax = wc / V;
+      for (int k = lane; k < kmax; k += 64) {
+        const bool two = (k + 32) < kmax;
+        const int k1 = two ? k + 32 : k;
+        Pack<V> a0[ROWS], a1[ROWS];
+#pragma unroll
+        for (int a = 0; a < ROWS; ++a) {
+          if (FUSE) {
+            Pack<V> g = pk_ld_stream<V>(G + roff[a] + (size_t)k * V);
+            Pack<V> e = pk_ld_stream<V>(E + roff[a] + (size_t)k * V);
+#pragma unroll
+            for (int x = 0; x < V; ++x) a0[a].v[x] = g.v[x] + e.v[x];
+          } else {
+            a0[a] = pk_ld_stream<V>(M + roff[a] + (size_t)k * V);
+          }
+        }
+#pragma unroll
+        for (int a = 0; a < ROWS; ++a) {
+          if (two) {
+            if (FUSE) {
+              Pack<V> g = pk_ld_stream<V>(G + roff[a] + (size_t)k1 * V);
+              Pack<V> e = pk_ld_stream<V>(E + roff[a] + (size_t)k1 * V);
+#pragma unroll
+              for (int x = 0; x < V; ++x) a1[a].v[x] = g.v[x] + e.v[x];
+            } else {
+              a1[a] = pk_ld_stream<V>(M + roff[a] + (size_t)k1 * V);
+            }
+          } else {
+            a1[a] = pk_zero<V>();
+          }
+        }
+        if (FUSE) {
+#pragma unroll
+          for (int a = 0; a < ROWS; ++a) {
+            if (rbase + a < nrows) {
+              pk_st_stream<V>(Mw + roff[a] + (size_t)k * V, a0[a]);
+              if (two) pk_st_stream<V>(Mw + roff[a] + (size_t)k1 * V, a1[a]);
+            }
+          }
+        }
+#pragma unroll
+        for (int c = 0; c < R; ++c) {
+          const Pack<V> q0 = pk_ld_shared<V>(Qs + c * pitch + k * V);
+          const Pack<V> q1 = pk_ld_shared<V>(Qs + c * pitch + k1 * V);
+#pragma unroll
+          for (int a = 0; a < ROWS; ++a) {
+#pragma unroll
+            for (int x = 0; x < V; ++x) {
+              acc[a][c] = fmaf(a0[a].v[x], q0.v[x], acc[a][c]);
+              acc[a][c] = fmaf(a1[a].v[x], q1.v[x], acc[a][c]);
+            }
+          }
+        }
+      }
+    }
+    if (live) {
+      float flat[NV];
+#pragma unroll
+      for (int a = 0; a < ROWS; ++a)
+#pragma unroll
+        for (int c = 0; c < R; ++c) flat[a * R + c] = acc[a][c];
+      const float tot = warp_fold<NV>(flat, lane);
+      constexpr int LPV = 32 / NV;  // lanes per value
+      if ((lane % LPV) == 0) {
+        const int idx = lane / LPV;
+        const int a = idx / R, c = idx % R;
+        if (rbase + a < nrows && c < r) P[(size_t)(row0 + rbase + a) * r + c] = tot;
+      }
+    }
+  }
+}
+
+template <int R, bool FUSE>
+__global__ void __launch_bounds__(kThreads, 2)
+k_p_from_m(DevPlan pl, PtrSlot ps, const float* __restrict__ q_mem, float* __restrict__ p_mem, float q_div) {
+  extern __shared__ __align__(16) float smem[];
+  const int4 t = pl.tiles1[blockIdx.x];
+  const MatDesc md = pl.mats[t.x];
+  const unsigned fl = ps.flags[t.x];
+  const float* M = ps.in[t.x];
+  const float* G = FUSE ? ps.g[t.x] : nullptr;
+  const float* E = FUSE ? ps.e[t.x] : nullptr;
+  float* Mw = FUSE ? const_cast<float*>(M) : nullptr;
+  const float* Q = q_mem + md.q_off;
+  float* P = p_mem + md.p_off;
+  const bool vec = (fl & kFlagInVec) && (!FUSE || (fl & kFlagGeVec));
+  if (vec)
+    p_tile<R, RowsK1<R>::v, 4, FUSE>(md, M, G, E, Mw, Q, P, t.y, t.z, pl.wc_cap, q_div, smem);
+  else
+    p_tile<R, RowsK1<R>::v, 1, FUSE>(md, M, G, E, Mw, Q, P, t.y, t.z, pl.wc_cap, q_div, smem);
+}
+
+// =======================================================================================
+// K2:  p_mem /= n_workers ; modified Gram-Schmidt of every P_i  (reducer.py:128,136-137,180-191)
+// One thread-block cluster per matrix; each CTA owns a contiguous slice of the rows and
+// every thread always touches the same rows, so P stays coherent without fences.  Step i
+// needs ONE cluster-wide reduction: ||col_i||^2 and the dots col_i . col_j (j > i) are
+// summed together, the projection coefficient is then dot / (norm + eps).  Column order and
+// normalise-then-project order are the reference's.  Partials travel through distributed
+// shared memory and are summed in a fixed order, so the result is deterministic.
+// =======================================================================================
+template <int R>
+__device__ __forceinline__ void orth_body(float* __restrict__ P, int n, int r, float world,
+                                          int crank, int csize, bool use_cluster) {
+  __shared__ float wsum[kOrthThreads / 32][R];
+  __shared__ float part[2][kOrthCluster][R];
+  __shared__ float tot_s[R];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int nthr = blockDim.x, nwarp = nthr >> 5;
+  const int per = (n + csize - 1) / csize;
+  const int lo = crank * per;
+  const int hi = (lo + per < n) ? lo + per : n;
+  const bool divide = world != 1.0f;
+
+  for (int i = 0; i < r; ++i) {
+    float s[R];
+#pragma unroll
+    for (int j = 0; j < R; ++j) s[j] = 0.f;
+    for (int row = lo + tid; row < hi; row += nthr) {
+      float* pr = P + (size_t)row * r;
+      float v[R];
+#pragma unroll
+      for (int j = 0; j < R; ++j) {
+        v[j] = 0.f;
+        if (j >= i && j < r) {
+          v[j] = pr[j];
+          if (i == 0 && divide) {
+            v[j] = v[j] / world;
+            pr[j] = v[j];
+          }
+        }
+      }
+      float vi = 0.f;
+#pragma unroll
+      for (int j = 0; j < R; ++j)
+        if (j == i) vi = v[j];
+#pragma unroll
+      for (int j = 0; j < R; ++j) s[j] = fmaf(vi, v[j], s[j]);
+    }
+#pragma unroll
+    for (int j = 0; j < R; ++j) {
+      if (j >= i && j < r) {
+        const float w = warp_sum(s[j]);
+        if (lane == 0) wsum[warp][j] = w;
+      }
+    }
+    __syncthreads();
+    const int par = i & 1;
+    if (use_cluster) {
+      if (tid < csize * R) {
+        const int dst = tid / R, j = tid % R;
+        if (j >= i && j < r) {
+          float t = 0.f;
+          for (int w = 0; w < nwarp; ++w) t += wsum[w][j];
+          cg::cluster_group cluster = cg::this_cluster();
+          float* remote = cluster.map_shared_rank(&part[0][0][0], dst);
+          remote[(par * kOrthCluster + crank) * R + j] = t;
+        }
+      }
+      cg::this_cluster().sync();
+    } else {
+      if (tid < R) {
+        const int j = tid;
+        if (j >= i && j < r) {
+          float t = 0.f;
+          for (int w = 0; w < nwarp; ++w) t += wsum[w][j];
+          part[par][0][j] = t;
+        }
+      }
+      __syncthreads();
+    }
+    float tot[R];
+#pragma unroll
+    for (int j = 0; j < R; ++j) {
+      tot[j] = 0.f;
+      if (j >= i && j < r)
+        for (int c = 0; c < csize; ++c) tot[j] += part[par][c][j];
+    }
+    float nrm2 = 0.f;
+#pragma unroll
+    for (int j = 0; j < R; ++j)
+      if (j == i) nrm2 = tot[j];
+    const float denom = sqrtf(nrm2) + 1e-8f;  // eps outside the root, reducer.py:186
+    float coef[R];
+#pragma unroll
+    for (int j = 0; j < R; ++j) coef[j] = (j > i && j < r) ? tot[j] / denom : 0.f;
+
+    for (int row = lo + tid; row < hi; row += nthr) {
+      float* pr = P + (size_t)row * r;
+      const float vi = pr[i] / denom;
+      pr[i] = vi;
+#pragma unroll
+      for (int j = 0; j < R; ++j)
+        if (j > i && j < r) pr[j] = fmaf(-coef[j], vi, pr[j]);
+    }
+    (void)tot_s;
+  }
+}
+
+template <int R>
+__global__ void __launch_bounds__(kOrthThreads)
+k_orthogonalize(DevPlan pl, float* __restrict__ p_mem, float world) {
+  cg::cluster_group cluster = cg::this_cluster();
+  const int csize = (int)cluster.num_blocks();
+  const int mat = blockIdx.x / csize;
+  const MatDesc md = pl.mats[mat];
+  orth_body<R>(p_mem + md.p_off, md.n, md.r, world, (int)cluster.block_rank(), csize, true);
+}
+
+// single matrix, single CTA: the module-level orthogonalize(matrix) of reducer.py:180-191
+template <int R>
+__global__ void __launch_bounds__(kOrthThreads)
+k_orthogonalize_one(float* __restrict__ mat, int n, int r) {
+  orth_body<R>(mat, n, r, 1.0f, 0, 1, false);
+}
+
+// =======================================================================================
+// K3:  Q = M^T P   (reducer.py:140-142) as a split-n reduction.
+// Tile = t3_rows rows x (cgw * cpt) columns.  Thread (rl, cg) owns `cpt` adjacent columns and
+// walks rows rl, rl + RL, ... accumulating cpt x R partial dot products in registers; the
+// P rows of the tile sit in shared memory and are read as broadcasts.  The RL row lanes are
+// combined through shared memory in fixed order and the tile's partial Q goes to the
+// workspace; k_q_reduce sums the row blocks in order (deterministic, no atomics).
+// =======================================================================================
+template <int R, int CPT, bool VECLD>
+__device__ __forceinline__ void q_tile(const MatDesc& md, const ColTile& t, const float* __restrict__ M,
+                                       const float* __restrict__ P, float* __restrict__ ws, float* smem) {
+  constexpr int U = 8;  // rows in flight per thread
+  constexpr int NV = CPT * R;
+  const int m = md.m, r = md.r, cgw = md.cgw;
+  const int RL = kThreads / cgw;
+  const int tid = threadIdx.x;
+  const int cgi = tid % cgw, rl = tid / cgw;
+  const int nrows = t.nrows;
+  float* Ps = smem;                       // [nrows][R]
+  float* red = smem + (size_t)md.t3_rows * R;  // [RL][NV][cgw + 1]
+
+  // stage P rows (contiguous nrows * r floats), widening r -> R with zeros
+  {
+    const float* src = P + (size_t)t.row0 * r;
+    const int total = nrows * R;
+    for (int e = tid; e < total; e += kThreads) {
+      const int i = e / R, c = e % R;
+      Ps[e] = (c < r) ? __ldg(src + (size_t)i * r + c) : 0.f;
+    }
+  }
+  __syncthreads();
+
+  const int col = t.col0 + cgi * CPT;
+  const bool active = col < m;  // CPT == 4 implies m % 4 == 0, so a group is all-in or all-out
+  float acc[CPT][R];
+#pragma unroll
+  for (int x = 0; x < CPT; ++x)
+#pragma unroll
+    for (int c = 0; c < R; ++c) acc[x][c] = 0.f;
+
+  if (active) {
+    const float* base = M + (size_t)t.row0 * m + col;
+    for (int i0 = rl; i0 < nrows; i0 += RL * U) {
+      float a[U][CPT];
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int i = i0 + u * RL;
+        if (i < nrows) {
+          const float* p = base + (size_t)i * m;
+          if (CPT == 4 && VECLD) {
+            const float4 v = ld_stream4(p);
+            a[u][0] = v.x; a[u][1 % CPT] = v.y; a[u][2 % CPT] = v.z; a[u][3 % CPT] = v.w;
+          } else {
+#pragma unroll
+            for (int x = 0; x < CPT; ++x) a[u][x] = ld_stream1(p + x);
+          }
+        } else {
+#pragma unroll
+          for (int x = 0; x < CPT; ++x) a[u][x] = 0.f;
+        }
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        int i = i0 + u * RL;
+        if (i > nrows - 1) i = nrows - 1;  // a == 0 there
+        const float* pp = Ps + (size_t)i * R;
+        float p[R];
+        if (R % 4 == 0) {
+#pragma unroll
+          for (int c = 0; c < R; c += 4) {
+            const float4 v = *reinterpret_cast<const float4*>(pp + c);
+            p[c] = v.x; p[(c + 1) % R] = v.y; p[(c + 2) % R] = v.z; p[(c + 3) % R] = v.w;
+          }
+        } else {
+#pragma unroll
+          for (int c = 0; c < R; ++c) p[c] = pp[c];
+        }
+#pragma unroll
+        for (int x = 0; x < CPT; ++x)
+#pragma unroll
+          for (int c = 0; c < R; ++c) acc[x][c] = fmaf(a[u][x], p[c], acc[x][c]);
+      }
+    }
+  }
+
+  // combine the RL row lanes: red[rl][v][cg], v = x * R + c
+  const int rp = cgw + 1;
+#pragma unroll
+  for (int x = 0; x < CPT; ++x)
+#pragma unroll
+    for (int c = 0; c < R; ++c) red[((size_t)rl * NV + x * R + c) * rp + cgi] = acc[x][c];
+  __syncthreads();
+
+  // partial layout in the workspace: [blk][m][r]
+  float* dst = ws + md.ws_off + (size_t)t.blk * m * r;
+  const int wcols = cgw * CPT;
+  const int total = wcols * R;
+  for (int e = tid; e < total; e += kThreads) {
+    const int j = e / R, c = e % R;  // tile-relative column, rank index
+    const int g = j / CPT, x = j % CPT;
+    const int cc = t.col0 + j;
+    if (cc < m && c < r) {
+      float s = 0.f;
+      for (int q = 0; q < RL; ++q) s += red[((size_t)q * NV + x * R + c) * rp + g];
+      dst[(size_t)cc * r + c] = s;
+    }
+  }
+}
+
+template <int R>
+__global__ void __launch_bounds__(kThreads, 2)
+k_q_from_mt(DevPlan pl, PtrSlot ps, const float* __restrict__ p_mem, float* __restrict__ ws) {
+  extern __shared__ __align__(16) float smem[];
+  const ColTile t = pl.tiles3[blockIdx.x];
+  const MatDesc md = pl.mats[t.mat];
+  const float* M = ps.in[t.mat];
+  const float* P = p_mem + md.p_off;
+  if (md.cpt == 4) {
+    if (ps.flags[t.mat] & kFlagInVec)
+      q_tile<R, 4, true>(md, t, M, P, ws, smem);
+    else
+      q_tile<R, 4, false>(md, t, M, P, ws, smem);
+  } else {
+    q_tile<R, 1, false>(md, t, M, P, ws, smem);
+  }
+}
+
+// stage 2: q_mem[e] = sum over row blocks, in block order
+__global__ void __launch_bounds__(kThreads)
+k_q_reduce(DevPlan pl, const float* __restrict__ ws, float* __restrict__ q_mem, long long q_total) {
+  const long long e = (long long)blockIdx.x * kThreads + threadIdx.x;
+  if (e >= q_total) return;
+  const int mat = find_segment(pl.q_pre, pl.n_mat, e);
+  const MatDesc md = pl.mats[mat];
+  const long long local = e - md.q_off;
+  const size_t stride = (size_t)md.m * md.r;
+  const float* src = ws + md.ws_off + local;
+  float s = 0.f;
+  int b = 0;
+  for (; b + 4 <= md.nblk3; b += 4) {
+    const float v0 = src[(size_t)b * stride];
+    const float v1 = src[(size_t)(b + 1) * stride];
+    const float v2 = src[(size_t)(b + 2) * stride];
+    const float v3 = src[(size_t)(b + 3) * stride];
+    s = ((s + v0) + v1) + v2 + v3;
+  }
+  for (; b < md.nblk3; ++b) s += src[(size_t)b * stride];
+  q_mem[e] = s;
+}
+
+// =======================================================================================
+// K4 + K5:  out = P (Q / n_workers)^T ; mem = M - out   (reducer.py:147,158-163), one sweep:
+// M is read once, out and mem are written once.  Same tiling as K1.
+// =======================================================================================
+template <int R, int ROWS, int V>
+__device__ __forceinline__ void fin_tile(const MatDesc& md, const float* __restrict__ M,
+                                         float* __restrict__ Out, float* __restrict__ Mem,
+                                         const float* __restrict__ Q, const float* __restrict__ P,
+                                         float world, int row0, int nrows, int wc_cap, float* Qs) {
+  const int m = md.m, r = md.r;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int nsets = (nrows + ROWS - 1) / ROWS;
+  const int nchunks = (m + wc_cap - 1) / wc_cap;
+  const int pitch = q_pitch(m < wc_cap ? m : wc_cap, R);
+
+  for (int ch = 0; ch < nchunks; ++ch) {
+    const int c0 = ch * wc_cap;
+    const int wc = (m - c0 < wc_cap) ? (m - c0) : wc_cap;
+    if (ch) __syncthreads();
+    stage_q<R>(Qs, Q, c0, wc, r, pitch, world);
+    __syncthreads();
+    const int kmax = wc / V;
+    for (int set = warp; set < nsets; set += kWarps) {
+      const int rbase = set * ROWS;
+      float p[ROWS][R];
+      size_t roff[ROWS];
+#pragma unroll
+      for (int a = 0; a < ROWS; ++a) {
+        int rr = rbase + a;
+        if (rr > nrows - 1) rr = nrows - 1;
+        roff[a] = (size_t)(row0 + rr) * m + c0;
+#pragma unroll
+        for (int c = 0; c < R; ++c) p[a][c] = (c < r) ? __ldg(P + (size_t)(row0 + rr) * r + c) : 0.f;
+      }
+      for (int k = lane; k < kmax; k += 64) {
+        const bool two = (k + 32) < kmax;
+        const int k1 = two ? k + 32 : k;
+        Pack<V> a0[ROWS], a1[ROWS];
+#pragma unroll
+        for (int a = 0; a < ROWS; ++a) a0[a] = pk_ld_stream<V>(M + roff[a] + (size_t)k * V);
+#pragma unroll
+        for (int a = 0; a < ROWS; ++a) a1[a] = two ? pk_ld_stream<V>(M + roff[a] + (size_t)k1 * V) : pk_zero<V>();
+        Pack<V> o0[ROWS], o1[ROWS];
+#pragma unroll
+        for (int a = 0; a < ROWS; ++a) { o0[a] = pk_zero<V>(); o1[a] = pk_zero<V>(); }
+#pragma unroll
+        for (int c = 0; c < R; ++c) {
+          const Pack<V> q0 = pk_ld_shared<V>(Qs + c * pitch + k * V);
+          const Pack<V> q1 = pk_ld_shared<V>(Qs + c * pitch + k1 * V);
+#pragma unroll
+          for (int a = 0; a < ROWS; ++a)
+#pragma unroll
+            for (int x = 0; x < V; ++x) {
+              o0[a].v[x] = fmaf(p[a][c], q0.v[x], o0[a].v[x]);
+              o1[a].v[x] = fmaf(p[a][c], q1.v[x], o1[a].v[x]);
+            }
+        }
+#pragma unroll
+        for (int a = 0; a < ROWS; ++a) {
+          if (rbase + a < nrows) {
+            Pack<V> e0, e1;
+#pragma unroll
+            for (int x = 0; x < V; ++x) { e0.v[x] = a0[a].v[x] - o0[a].v[x]; e1.v[x] = a1[a].v[x] - o1[a].v[x]; }
+            pk_st_stream<V>(Out + roff[a] + (size_t)k * V, o0[a]);
+            pk_st_stream<V>(Mem + roff[a] + (size_t)k * V, e0);
+            if (two) {
+              pk_st_stream<V>(Out + roff[a] + (size_t)k1 * V, o1[a]);
+              pk_st_stream<V>(Mem + roff[a] + (size_t)k1 * V, e1);
+            }
+          }
+        }
+      }
+    }
+  }
+}
+
+template <int R>
+__global__ void __launch_bounds__(kThreads, 2)
+k_finalize(DevPlan pl, PtrSlot ps, const float* __restrict__ p_mem, const float* __restrict__ q_mem, float world) {
+  extern __shared__ __align__(16) float smem[];
+  const int4 t = pl.tiles4[blockIdx.x];
+  const MatDesc md = pl.mats[t.x];
+  const unsigned fl = ps.flags[t.x];
+  const float* M = ps.in[t.x];
+  float* Out = ps.out[t.x];
+  float* Mem = ps.mem[t.x];
+  const float* Q = q_mem + md.q_off;
+  const float* P = p_mem + md.p_off;
+  if ((fl & kFlagInVec) && (fl & kFlagOutVec))
+    fin_tile<R, RowsK4<R>::v, 4>(md, M, Out, Mem, Q, P, world, t.y, t.z, pl.wc_cap, smem);
+  else
+    fin_tile<R, RowsK4<R>::v, 1>(md, M, Out, Mem, Q, P, world, t.y, t.z, pl.wc_cap, smem);
+}
+
+// =======================================================================================
+// K6: flat-buffer gather / scatter of the <=1-D tensors (tensor_buffer.py:19,34-36) as one
+// kernel over a pointer table; T is the element word (1/2/4/8 bytes) so TensorBuffer keeps
+// the upstream "dtype follows the inputs" behaviour bit-exactly.
+// =======================================================================================
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+k_gather(const long long* __restrict__ pre, int n, const void* const* __restrict__ src, T* __restrict__ flat,
+         long long total) {
+  const long long e = (long long)blockIdx.x * kThreads + threadIdx.x;
+  if (e >= total) return;
+  const int t = find_segment(pre, n, e);
+  flat[e] = static_cast<const T*>(src[t])[e - __ldg(pre + t)];
+}
+
+template <typename T>
+__global__ void __launch_bounds__(kThreads)
+k_scatter(const long long* __restrict__ pre, int n, const T* __restrict__ flat, void* const* __restrict__ dst,
+          long long total) {
+  const long long e = (long long)blockIdx.x * kThreads + threadIdx.x;
+  if (e >= total) return;
+  const int t = find_segment(pre, n, e);
+  static_cast<T*>(dst[t])[e - __ldg(pre + t)] = flat[e];
+}
+
+// K6b: vec_out = flat / n_workers (reducer.py:167-168) and q_mem /= n_workers (reducer.py:147)
+__global__ void __launch_bounds__(kThreads)
+k_finish(DevPlan pl, PtrSlot ps, const float* __restrict__ flat, long long v_total, float* __restrict__ q_mem,
+         long long q_total, float world) {
+  const long long e = (long long)blockIdx.x * kThreads + threadIdx.x;
+  if (e < v_total) {
+    const int t = find_segment(pl.v_pre, pl.n_vec, e);
+    float v = flat[e];
+    if (world != 1.0f) v = v / world;
+    ps.vout[t][e - __ldg(pl.v_pre + t)] = v;
+  } else if (e - v_total < q_total) {
+    q_mem[e - v_total] = q_mem[e - v_total] / world;
+  }
+}
+
+}  // namespace psgd

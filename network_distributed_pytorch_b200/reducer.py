@@ -1,0 +1,220 @@
+"""Host mirror of the upstream ``reducer.py`` (ddp_powersgd_guide_cifar10/reducer.py, same file
+under ddp_powersgd_distillBERT_IMDb/): same class names, constructor and ``reduce`` signature,
+same public attributes, same packed ``p_memory`` / ``q_memory`` layout, same returned bit count
+-- but every per-layer PyTorch op of the upstream loops is replaced by one grouped sm_100a
+kernel per phase behind the C ABI in include/psgd_b200.h.
+
+What stays on the host, and why:
+  * the seed stream (reducer.py:8-12, :37): numpy's legacy RandomState has no skip-ahead, so the
+    128 Mi-draw burn is replayed (chunked, cached per seed) to reach the same Q seeds;
+  * Q initialisation (reducer.py:36-38): issued as the very same ``torch.manual_seed`` +
+    ``torch.randn`` calls so Q *and* the side effect on the global generator match upstream;
+  * the three SUM all-reduces (reducer.py:126, :132, :145) through ``torch.distributed``.
+"""
+import numpy as np
+import torch
+
+from . import tensor_buffer as tb  # noqa: F401  (upstream: ``import tensor_buffer as tb``)
+
+_BURN_DRAWS = 128 * 1024 * 1024  # reducer.py:9-11
+_burned_states = {}
+
+
+def _burned_random_state(seed):
+    """np.random.RandomState(seed) after the 128 Mi ``randn`` draws of reducer.py:8-12."""
+    state = _burned_states.get(seed)
+    if state is None:
+        rng = np.random.RandomState(seed)
+        left, chunk = _BURN_DRAWS, 4 * 1024 * 1024
+        while left:  # chunking keeps the stream identical (the spare gaussian is part of the state)
+            k = min(left, chunk)
+            rng.randn(k)
+            left -= k
+        state = _burned_states[seed] = rng.get_state()
+    rng = np.random.RandomState()
+    rng.set_state(state)
+    return rng
+
+
+class Reducer:
+    """reducer.py:6-23."""
+
+    def __init__(self, random_seed, device, _engine=None):
+        self._random_seed = random_seed
+        self.rng = _burned_random_state(random_seed)
+        self._precalc = None
+        if torch.distributed.is_available():
+            self.n_workers = torch.distributed.get_world_size()
+            self.rank = torch.distributed.get_rank()
+        else:
+            self.n_workers = 1
+            self.rank = 0
+        self.device = device
+        if _engine is None:
+            from .engine import CudaEngine
+
+            _engine = CudaEngine(device)  # raises without CUDA / without the built library
+        self._engine = _engine
+
+    @property
+    def precalc_numbers(self):
+        """Upstream keeps 128 Mi normals on the device and never reads them (reducer.py:10-12);
+        here they are regenerated on first access instead of pinning 512 MiB of HBM."""
+        if self._precalc is None:
+            rng = np.random.RandomState(self._random_seed)
+            self._precalc = torch.from_numpy(rng.randn(_BURN_DRAWS)).to(self.device).type(torch.float32)
+        return self._precalc
+
+    def reduce(self, grad_in, grad_out, memory_out):
+        """Return communicated bits"""
+        raise NotImplementedError()
+
+
+class PowerSGDReducer(Reducer):
+    """reducer.py:25-170.  ``n_power_iterations`` must be 0 as upstream (reducer.py:30); extra
+    subspace iterations are available through the keyword-only ``extra_power_iterations``."""
+
+    def __init__(self, random_seed, device, n_power_iterations=0, reuse_query=True, rank=1, *,
+                 extra_power_iterations=0, _engine=None):
+        super().__init__(random_seed, device, _engine=_engine)
+        assert n_power_iterations == 0
+        self.rank = rank
+        self.p_memory = None
+        self.q_memory = None
+        self.reuse_query = reuse_query
+        self.extra_power_iterations = int(extra_power_iterations)
+        self._plans = {}
+        self._flat = {}
+
+    def _set_random(self, vector):
+        # reducer.py:36-38, verbatim semantics including the global reseed
+        torch.manual_seed(self.rng.randint(1_000_000_000))
+        vector.data[:] = torch.randn(*vector.shape, device=self.device)
+
+    # ---------------------------------------------------------------------------------------
+    def _plan_for(self, grad_in, mats, vecs):
+        key = tuple(tuple(t.shape) for t in grad_in)
+        plan = self._plans.get(key)
+        if plan is None:
+            dims = []
+            for t in mats:
+                n = t.shape[0]
+                dims.append((n, t.nelement() // n if n else 0))
+            plan = self._engine.make_plan(dims, self.rank, [t.nelement() for t in vecs])
+            self._plans[key] = plan
+            self._flat[key] = self._engine.empty(max(plan.vec_elems, 1))[: plan.vec_elems]
+        return plan, self._flat[key]
+
+    def _check(self, lists):
+        for lst in lists:
+            for t in lst:
+                if t.dtype != torch.float32:
+                    raise RuntimeError(f"PowerSGDReducer expects float32 tensors, got {t.dtype}")
+                if not t.is_contiguous():
+                    # upstream fails in tensor.view(tensor.shape[0], -1) (reducer.py:75)
+                    raise RuntimeError("view size is not compatible with input tensor's size and stride: "
+                                       "PowerSGDReducer needs contiguous tensors")
+
+    def reduce(self, grad_in, grad_out, memory_out):
+        """
+        grad_in, grad_out, memory_out : lists of same-shaped fp32 tensors on ``device``
+        return total communicated bits
+        """
+        return self._reduce(grad_in, grad_out, memory_out, None, None)
+
+    def _reduce(self, grad_in, grad_out, memory_out, fuse_g, fuse_e):
+        if not (len(grad_in) == len(grad_out) == len(memory_out)):
+            raise ValueError("grad_in, grad_out and memory_out must have the same length")
+        self._check((grad_in, grad_out, memory_out))
+        # reducer.py:53-62
+        vec_idx = [i for i, t in enumerate(grad_in) if t.ndimension() <= 1]
+        mat_idx = [i for i, t in enumerate(grad_in) if t.ndimension() > 1]
+        if not vec_idx:
+            # upstream: TensorBuffer([]) -> torch.cat of an empty list (tensor_buffer.py:19)
+            raise RuntimeError("torch.cat(): expected a non-empty list of Tensors (no <=1-D tensor to pack)")
+        mats = [grad_in[i] for i in mat_idx]
+        vecs = [grad_in[i] for i in vec_idx]
+        plan, flat = self._plan_for(grad_in, mats, vecs)
+        world = self.n_workers
+        bits_communicated = 0
+
+        # reducer.py:68-84
+        mem_uninitialized = self.p_memory is None
+        if mem_uninitialized:
+            self.p_memory = self._engine.empty(plan.p_elems)
+            self.q_memory = self._engine.empty(plan.q_elems)
+        elif self.p_memory.nelement() != plan.p_elems or self.q_memory.nelement() != plan.q_elems:
+            raise RuntimeError("gradient shapes changed after p_memory/q_memory were allocated")
+
+        # reducer.py:101-111
+        if not (self.reuse_query and not mem_uninitialized):
+            for info in plan.mats:
+                q = self.q_memory[info["q_off"] : info["q_off"] + info["m"] * info["r"]].view(info["m"], info["r"])
+                self._set_random(q)
+
+        plan.set_ptrs(mats, [grad_out[i] for i in mat_idx], [memory_out[i] for i in mat_idx],
+                      vecs, [grad_out[i] for i in vec_idx],
+                      [fuse_g[i] for i in mat_idx] if fuse_g is not None else None,
+                      [fuse_e[i] for i in mat_idx] if fuse_e is not None else None)
+
+        # [For Rank 1] the flat buffer does not depend on P: pack and start its all-reduce first
+        # (upstream starts it after step 4, reducer.py:131-133; the sum is the same)
+        plan.pack_vec(flat)
+        rank1_handler = None
+        if world > 1:
+            rank1_handler = torch.distributed.all_reduce(flat, async_op=True)
+        bits_communicated += 8 * flat.nelement() * flat.element_size()
+
+        for it in range(self.extra_power_iterations + 1):
+            # Step 3 (reducer.py:121-123) P <- M Q
+            plan.p_from_m(self.p_memory, self.q_memory, fuse_add=(fuse_g is not None and it == 0),
+                          q_div=(world if it > 0 else 1.0))
+            # Step 4 (reducer.py:126-128) ALL_REDUCE_MEAN(P); the divide is folded into step 5
+            all_reduce(self.p_memory)
+            bits_communicated += n_bits(self.p_memory)
+            # Step 5 (reducer.py:136-137) P_hat <- ORTHOGONALIZE(P / n_workers)
+            plan.orthogonalize(self.p_memory, world)
+            # Step 6 (reducer.py:140-142) Q <- M^T P_hat
+            plan.q_from_mt(self.p_memory, self.q_memory)
+            # Step 7 (reducer.py:145-147) ALL_REDUCE_MEAN(Q); the divide is applied while Q is staged
+            all_reduce(self.q_memory)
+            bits_communicated += n_bits(self.q_memory)
+
+        # Step 8 + 9 (reducer.py:158-163) decompress and memorise the local error in one sweep
+        plan.finalize(self.p_memory, self.q_memory, world)
+
+        # [For Rank 1] (reducer.py:166-168) wait, mean, scatter; q_memory becomes the mean in place
+        if rank1_handler is not None:
+            rank1_handler.wait()
+        plan.finish(flat, self.q_memory if world > 1 else None, world)
+        return bits_communicated
+
+
+def orthogonalize(matrix, eps=torch.tensor(1e-8)):
+    """reducer.py:180-191: in-place modified Gram-Schmidt of an (n, r) fp32 CUDA matrix."""
+    if matrix.ndimension() != 2:
+        raise RuntimeError("orthogonalize expects a 2-D matrix")
+    if float(eps) != float(torch.tensor(1e-8)):
+        raise NotImplementedError("the CUDA kernel hard-codes the upstream default eps=1e-8")
+    if matrix.device.type != "cuda" or matrix.dtype != torch.float32:
+        raise RuntimeError("orthogonalize (B200 build) needs a float32 CUDA matrix; there is no CPU fallback")
+    from .engine import CudaEngine
+
+    eng = CudaEngine(matrix.device)
+    if matrix.is_contiguous():
+        eng.orthogonalize_matrix(matrix)
+    else:  # upstream works on any strides; go through a packed copy
+        tmp = matrix.contiguous()
+        eng.orthogonalize_matrix(tmp)
+        matrix.copy_(tmp)
+
+
+def all_reduce(*args, **kwargs):
+    """reducer.py:193-195."""
+    if torch.distributed.is_available() and torch.distributed.get_world_size() > 1:
+        return torch.distributed.all_reduce(*args, **kwargs)
+
+
+def n_bits(tensor):
+    """reducer.py:197-198."""
+    return 8 * tensor.nelement() * tensor.element_size()

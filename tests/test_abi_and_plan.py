@@ -1,0 +1,104 @@
+"""The C-ABI library without a GPU: it loads, exports every symbol include/psgd_b200.h declares,
+and its host-only plan reproduces the upstream packed layout and tiles every matrix exactly."""
+import ctypes
+import os
+import re
+
+import numpy as np
+import pytest
+
+from network_distributed_pytorch_b200 import _lib, workloads
+from network_distributed_pytorch_b200.build import build
+from network_distributed_pytorch_b200.engine import host_plan
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def lib():
+    build()
+    return _lib.load()
+
+
+def header_symbols():
+    text = open(os.path.join(ROOT, "include", "psgd_b200.h")).read()
+    text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
+    return sorted(set(re.findall(r"\b(psgd_[a-z0-9_]+)\s*\(", text)))
+
+
+def test_every_declared_symbol_is_exported_and_bound(lib):
+    names = header_symbols()
+    assert len(names) >= 20
+    for n in names:
+        assert hasattr(lib, n), f"{n} declared in psgd_b200.h but not exported"
+    assert set(names) == set(_lib.SIGNATURES), "ctypes table and header disagree"
+    assert lib.psgd_abi_version() == 1
+
+
+def test_compute_entry_points_fail_loudly_on_host_only_plan(lib):
+    plan = host_plan([(8, 6)], 2, [3])
+    rc = lib.psgd_p_from_m(plan._h, None, None, 0, ctypes.c_float(1.0), None)
+    assert rc != 0 and b"host-only" in lib.psgd_last_error()
+    h = ctypes.c_void_p()
+    assert lib.psgd_plan_create(1, _lib.i64_array([4]), _lib.i64_array([4]), 0, 0, _lib.i64_array([]), -1,
+                                ctypes.byref(h)) != 0  # rank 0 rejected
+    assert lib.psgd_plan_create(1, _lib.i64_array([64]), _lib.i64_array([64]), 33, 0, _lib.i64_array([]), -1,
+                                ctypes.byref(h)) != 0  # beyond PSGD_MAX_RANK
+    assert b"PSGD_MAX_RANK" in lib.psgd_last_error()
+
+
+def split(shapes):
+    mats = [(s[0], int(np.prod(s[1:]))) for s in shapes if len(s) > 1]
+    vecs = [int(np.prod(s)) if len(s) else 1 for s in shapes if len(s) <= 1]
+    return mats, vecs
+
+
+@pytest.mark.parametrize("name,rank", [("resnet18", 2), ("distilbert", 4), ("distilbert", 1), ("resnet50", 4),
+                                       ("bert-large", 8), ("resnet152", 4), ("distilbert", 16), ("distilbert", 3)])
+def test_packed_layout_and_tiles(lib, name, rank):
+    shapes = workloads.WORKLOADS[name]()
+    mats, vecs = split(shapes)
+    st = workloads.stats(shapes, rank)
+    plan = host_plan(mats, rank, vecs)
+    assert plan.p_elems == st["e_p"] and plan.q_elems == st["e_q"] and plan.vec_elems == st["e_1"]
+    po = qo = 0
+    for (n, m), info in zip(mats, plan.mats):  # reducer.py:86-98 running offsets, no padding
+        r = min(n, m, rank)
+        assert (info["n"], info["m"], info["r"], info["p_off"], info["q_off"]) == (n, m, r, po, qo)
+        po += n * r
+        qo += m * r
+    # row tiles of K1 / K4 partition the rows of every matrix exactly once
+    for phase in (_lib.PHASE_P_FROM_M, _lib.PHASE_FINALIZE):
+        cover = [0] * len(mats)
+        for mat, row0, nrows, _, ncols, _ in plan.tiles(phase):
+            assert row0 == cover[mat] and nrows > 0 and ncols == mats[mat][1]
+            cover[mat] += nrows
+        assert cover == [n for n, _ in mats]
+    # K3 tiles partition (rows x columns); workspace slices do not overlap
+    seen = {}
+    for mat, row0, nrows, col0, ncols, blk in plan.tiles(_lib.PHASE_Q_FROM_MT):
+        assert nrows > 0 and ncols > 0
+        seen.setdefault(mat, []).append((row0, nrows, col0, ncols, blk))
+    ws_end = 0
+    for i, ((n, m), info) in enumerate(zip(mats, plan.mats)):
+        area = sum(t[1] * t[3] for t in seen[i])
+        assert area == n * m
+        assert max(t[4] for t in seen[i]) + 1 == info["row_blocks"]
+        assert info["ws_off"] >= ws_end and info["ws_off"] % 4 == 0
+        ws_end = info["ws_off"] + info["row_blocks"] * m * info["r"]
+    assert plan.workspace_bytes >= 4 * ws_end
+
+
+def test_ragged_and_degenerate_shapes(lib):
+    mats = [(1, 5), (5, 1), (64, 147), (3, 7), (1000, 12), (2, 4096 * 3)]
+    plan = host_plan(mats, 4, [1, 7])
+    assert [d["r"] for d in plan.mats] == [1, 1, 4, 3, 4, 2]
+    for phase in (_lib.PHASE_P_FROM_M, _lib.PHASE_FINALIZE):
+        rows = {}
+        for mat, row0, nrows, *_ in plan.tiles(phase):
+            rows[mat] = rows.get(mat, 0) + nrows
+        assert rows == {i: n for i, (n, _) in enumerate(mats)}
+    cols = {}
+    for mat, row0, nrows, col0, ncols, blk in plan.tiles(_lib.PHASE_Q_FROM_MT):
+        cols[mat] = cols.get(mat, 0) + nrows * ncols
+    assert cols == {i: n * m for i, (n, m) in enumerate(mats)}

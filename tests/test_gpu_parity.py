@@ -1,0 +1,281 @@
+"""Parity of the CUDA hot path (through the C ABI) with the oracle and with the vectors produced by the
+real upstream reducer.  Tolerance: <= 1e-5 relative Frobenius error per tensor (BASELINE.json), packed
+layouts and returned bit counts exact."""
+import numpy as np
+import pytest
+import torch
+
+from tests.helpers import GOLDEN_CASES, Golden, flatten, per_tensor_rel_err, rel_err, unflatten
+
+pytestmark = pytest.mark.gpu
+TOL = 1e-5
+
+
+@pytest.fixture(scope="module", autouse=True)
+def group():
+    from tests.gpu_common import ensure_group
+
+    ensure_group()
+    yield
+
+
+def _inject_queries(red, per_step_qinit):
+    """Make _set_random hand out the reference's recorded draws instead of device randn."""
+    state = {"buf": None, "off": 0}
+
+    def fake(vector):
+        red.rng.randint(1_000_000_000)  # keep the seed stream moving as upstream would
+        k = vector.nelement()
+        vector.data[:] = state["buf"][state["off"] : state["off"] + k].view(vector.shape)
+        state["off"] += k
+
+    red._set_random = fake
+
+    def arm(qinit):
+        state["buf"] = torch.from_numpy(qinit).to(red.device)
+        state["off"] = 0
+
+    return arm
+
+
+@pytest.mark.parametrize("name", [c for c in GOLDEN_CASES if c.startswith("w1")])
+def test_reference_vectors_world1(name):
+    from network_distributed_pytorch_b200.reducer import PowerSGDReducer
+
+    g = Golden(name)
+    dev = torch.device("cuda", 0)
+    red = PowerSGDReducer(g.seed, dev, 0, g.reuse, g.rank)
+    arm = _inject_queries(red, None)
+    mem = [torch.zeros(s, device=dev) for s in g.shapes]
+    for step in range(g.steps):
+        arm(g.get(0, step, "qinit"))
+        gin = unflatten(g.get(0, step, "in"), g.shapes, device=dev)
+        gout = [torch.zeros(s, device=dev) for s in g.shapes]
+        bits = red.reduce(gin, gout, mem)
+        torch.cuda.synchronize()
+        assert bits == int(g.get(0, step, "bits"))
+        assert red.p_memory.nelement() == g.get(0, step, "p").size  # packed layout: same size, same order
+        assert rel_err(red.p_memory.cpu().numpy(), g.get(0, step, "p")) < TOL
+        assert rel_err(red.q_memory.cpu().numpy(), g.get(0, step, "q")) < TOL
+        for key, lst in (("out", gout), ("mem", mem)):
+            errs = per_tensor_rel_err(flatten(lst), g.get(0, step, key), g.shapes)
+            assert max(errs) < TOL, (name, step, key, errs)
+        # continue from the reference's memory so every step is a single-step comparison
+        for t, ref in zip(mem, unflatten(g.get(0, step, "mem"), g.shapes, device=dev)):
+            t.copy_(ref)
+
+
+@pytest.mark.parametrize("name", [c for c in GOLDEN_CASES if c.startswith("w2")])
+def test_reference_vectors_world2_emulated_on_one_gpu(name):
+    """Two ranks of the real reference vs two plans on one GPU with the all-reduce emulated by a sum:
+    checks the folded /n_workers divides (orthogonalize, finalize, finish) against upstream."""
+    from network_distributed_pytorch_b200.engine import CudaEngine
+
+    g = Golden(name)
+    dev = torch.device("cuda", 0)
+    eng = CudaEngine(dev)
+    mat_idx = [i for i, s in enumerate(g.shapes) if len(s) > 1]
+    vec_idx = [i for i, s in enumerate(g.shapes) if len(s) <= 1]
+    dims = [(g.shapes[i][0], int(np.prod(g.shapes[i][1:]))) for i in mat_idx]
+    plans = [eng.make_plan(dims, g.rank, [int(np.prod(g.shapes[i])) for i in vec_idx]) for _ in range(2)]
+    p = [eng.empty(plans[0].p_elems) for _ in range(2)]
+    q = [eng.empty(plans[0].q_elems) for _ in range(2)]
+    flat = [eng.empty(plans[0].vec_elems) for _ in range(2)]
+    mem = [[torch.zeros(s, device=dev) for s in g.shapes] for _ in range(2)]
+    for step in range(g.steps):
+        qinit = g.get(0, step, "qinit")
+        if qinit.size:
+            for k in range(2):
+                q[k].copy_(torch.from_numpy(qinit))
+        gin = [unflatten(g.get(k, step, "in"), g.shapes, device=dev) for k in range(2)]
+        gout = [[torch.zeros(s, device=dev) for s in g.shapes] for _ in range(2)]
+        for k in range(2):
+            plans[k].set_ptrs([gin[k][i] for i in mat_idx], [gout[k][i] for i in mat_idx], [mem[k][i] for i in mat_idx],
+                              [gin[k][i] for i in vec_idx], [gout[k][i] for i in vec_idx])
+            plans[k].pack_vec(flat[k])
+            plans[k].p_from_m(p[k], q[k])
+        psum = p[0] + p[1]
+        fsum = flat[0] + flat[1]
+        for k in range(2):
+            p[k].copy_(psum)
+            plans[k].orthogonalize(p[k], 2)
+            plans[k].q_from_mt(p[k], q[k])
+        qsum = q[0] + q[1]
+        for k in range(2):
+            q[k].copy_(qsum)
+            plans[k].finalize(p[k], q[k], 2)
+            plans[k].finish(fsum, q[k], 2)
+        torch.cuda.synchronize()
+        assert torch.equal(p[0], p[1]) and torch.equal(q[0], q[1])
+        assert rel_err(p[0].cpu().numpy(), g.get(0, step, "p")) < TOL
+        assert rel_err(q[0].cpu().numpy(), g.get(0, step, "q")) < TOL
+        for k in range(2):
+            for key, lst in (("out", gout[k]), ("mem", mem[k])):
+                errs = per_tensor_rel_err(flatten(lst), g.get(k, step, key), g.shapes)
+                assert max(errs) < TOL, (name, step, key, k, errs)
+            for t, ref in zip(mem[k], unflatten(g.get(k, step, "mem"), g.shapes, device=dev)):
+                t.copy_(ref)
+
+
+SHAPE_SETS = {
+    "tiny": [(8, 3, 3, 3), (6,), (16, 8), (16,), (1, 5), (5, 1), (12, 20), (3,)],
+    "odd_columns": [(64, 3, 7, 7), (64,), (33, 27), (5,), (130, 1), (1, 130), (7, 13), (2,)],
+    "transformer_slice": [(512, 768), (768,), (768, 768), (768,), (3072, 768), (3072,), (768, 3072), (2, 768), (2,)],
+    "tall": [(30522, 64), (64,), (4099, 132), (1,)],
+    "wide_chunked": [(9, 25088), (9,), (40, 30000), (3,), (70, 13001), (2,)],
+    "conv": [(128, 64, 3, 3), (128,), (256, 128, 1, 1), (256,), (512, 512, 3, 3), (512,), (1000, 512), (1000,)],
+}
+
+
+@pytest.mark.parametrize("rank", [1, 2, 3, 4, 8, 16, 32])
+@pytest.mark.parametrize("setname", list(SHAPE_SETS))
+def test_matches_oracle_single_step(setname, rank):
+    from tests.gpu_common import run_pair
+
+    if setname in ("tall", "wide_chunked", "conv") and rank in (3, 32):
+        pytest.skip("covered by the other ranks; keeps the suite short")
+    res = run_pair(SHAPE_SETS[setname], rank, steps=1)[0]
+    assert res["send_equal"]
+    assert max(res["out"]) < TOL and max(res["mem"]) < TOL, res
+    assert res["p"] < TOL and res["q"] < TOL, res
+
+
+@pytest.mark.parametrize("reuse", [True, False])
+def test_three_steps_with_error_feedback(reuse):
+    from tests.gpu_common import run_pair
+
+    for res in run_pair(SHAPE_SETS["transformer_slice"], 4, steps=3, reuse=reuse):
+        assert max(res["out"]) < TOL and max(res["mem"]) < TOL and res["p"] < TOL and res["q"] < TOL, res
+
+
+@pytest.mark.parametrize("offset", [1, 2, 3])
+def test_unaligned_tensors_take_the_scalar_path(offset):
+    from tests.gpu_common import run_pair
+
+    res = run_pair(SHAPE_SETS["tiny"] + [(96, 256), (256,)], 4, steps=1, offset_elems=offset)[0]
+    assert max(res["out"]) < TOL and max(res["mem"]) < TOL and res["p"] < TOL and res["q"] < TOL, res
+
+
+def test_extra_power_iteration_matches_oracle():
+    from tests.gpu_common import run_pair
+
+    res = run_pair(SHAPE_SETS["transformer_slice"], 4, steps=1, extra=1)[0]
+    assert max(res["out"]) < TOL and max(res["mem"]) < TOL and res["p"] < TOL and res["q"] < TOL, res
+
+
+def test_steep_spectrum_single_step():
+    from tests.gpu_common import run_pair
+
+    res = run_pair([(768, 768), (768,), (1024, 256), (4,)], 8, steps=1, scale_cols=True)[0]
+    assert max(res["out"]) < TOL and max(res["mem"]) < TOL, res
+
+
+def test_full_size_distilbert_properties():
+    """BASELINE config 2 at full size: size-independent properties instead of an element-wise oracle."""
+    from network_distributed_pytorch_b200 import workloads
+    from network_distributed_pytorch_b200.reducer import PowerSGDReducer
+
+    dev = torch.device("cuda", 0)
+    shapes = workloads.distilbert()
+    st = workloads.stats(shapes, 4)
+    gen = torch.Generator(device=dev).manual_seed(1000)
+    gin = [torch.randn(s, device=dev, generator=gen) for s in shapes]
+    keep = [t.clone() for t in gin]
+    gout = [torch.zeros(s, device=dev) for s in shapes]
+    mem = [torch.zeros(s, device=dev) for s in shapes]
+    red = PowerSGDReducer(714, dev, 0, True, 4)
+    bits = red.reduce(gin, gout, mem)
+    torch.cuda.synchronize()
+    assert bits == st["bits"] == 17022400
+    assert red.p_memory.nelement() == st["e_p"] and red.q_memory.nelement() == st["e_q"]
+    po = qo = 0
+    for t, k, o, e in zip(gin, keep, gout, mem):
+        assert torch.equal(t, k)  # grad_in is read-only
+        if t.ndimension() <= 1:
+            assert torch.equal(o, t) and not e.any()  # world 1: mean of one; memory untouched
+            continue
+        n, m = t.shape[0], t.nelement() // t.shape[0]
+        r = min(n, m, 4)
+        P = red.p_memory[po : po + n * r].view(n, r)
+        Q = red.q_memory[qo : qo + m * r].view(m, r)
+        po += n * r
+        qo += m * r
+        M = t.view(n, m)
+        # out + mem reconstructs M (mem = M - out in fp32: one rounding)
+        assert rel_err((o + e).cpu().numpy(), t.cpu().numpy()) < 1e-6
+        # P_hat has orthonormal columns, Q = M^T P_hat, out = P_hat Q^T (checked in fp64 on the GPU)
+        Pd, Qd, Md = P.double(), Q.double(), M.double()
+        assert torch.allclose(Pd.t() @ Pd, torch.eye(r, device=dev, dtype=torch.float64), atol=1e-5)
+        assert rel_err((Md.t() @ Pd).cpu().numpy(), Qd.cpu().numpy()) < TOL
+        assert rel_err((Pd @ Qd.t()).cpu().numpy(), o.view(n, m).cpu().numpy()) < TOL
+    # determinism: a second reducer on the same inputs reproduces every bit
+    red2 = PowerSGDReducer(714, dev, 0, True, 4)
+    gout2 = [torch.zeros(s, device=dev) for s in shapes]
+    mem2 = [torch.zeros(s, device=dev) for s in shapes]
+    red2.reduce(gin, gout2, mem2)
+    torch.cuda.synchronize()
+    assert torch.equal(red.p_memory, red2.p_memory) and torch.equal(red.q_memory, red2.q_memory)
+    assert all(torch.equal(a, b) for a, b in zip(gout, gout2)) and all(torch.equal(a, b) for a, b in zip(mem, mem2))
+
+
+def test_fused_add_entry_point():
+    """psgd_p_from_m(fuse_add=1): M = grad + err is formed inside K1 and stored to mat_in."""
+    from network_distributed_pytorch_b200.engine import CudaEngine
+
+    dev = torch.device("cuda", 0)
+    eng = CudaEngine(dev)
+    dims = [(96, 256), (33, 27), (40, 8000)]
+    plan = eng.make_plan(dims, 4, [5])
+    torch.manual_seed(5)
+    g = [torch.randn(d, device=dev) for d in dims]
+    e = [torch.randn(d, device=dev) for d in dims]
+    send = [torch.zeros(d, device=dev) for d in dims]
+    out = [torch.zeros(d, device=dev) for d in dims]
+    mem = [torch.zeros(d, device=dev) for d in dims]
+    v = [torch.randn(5, device=dev)]
+    vo = [torch.zeros(5, device=dev)]
+    p = eng.empty(plan.p_elems)
+    q = torch.randn(plan.q_elems, device=dev)
+    plan.set_ptrs(send, out, mem, v, vo, grad=g, err=e)
+    plan.p_from_m(p, q, fuse_add=True)
+    torch.cuda.synchronize()
+    for a, b, s, info in zip(g, e, send, plan.mats):
+        assert torch.equal(s, a + b)
+        n, m, r = info["n"], info["m"], info["r"]
+        want = (a + b).double() @ q[info["q_off"] : info["q_off"] + m * r].view(m, r).double()
+        got = p[info["p_off"] : info["p_off"] + n * r].view(n, r)
+        assert rel_err(got.cpu().numpy(), want.cpu().numpy()) < TOL
+
+
+def test_orthogonalize_module_function():
+    from network_distributed_pytorch_b200.reducer import orthogonalize
+    from oracle.powersgd_oracle import gram_schmidt_inplace
+
+    dev = torch.device("cuda", 0)
+    for n, r in [(1, 1), (7, 3), (768, 4), (30522, 8), (5000, 32)]:
+        torch.manual_seed(n)
+        a = torch.randn(n, r)
+        b = a.clone().to(dev)
+        gram_schmidt_inplace(a)
+        assert orthogonalize(b) is None
+        assert rel_err(b.cpu().numpy(), a.numpy()) < TOL, (n, r)
+
+
+def test_timing_and_launch_counter():
+    from network_distributed_pytorch_b200.engine import CudaEngine
+
+    dev = torch.device("cuda", 0)
+    eng = CudaEngine(dev)
+    plan = eng.make_plan([(256, 256)], 4, [16])
+    t = [torch.randn(256, 256, device=dev)]
+    o, m = [torch.zeros_like(t[0])], [torch.zeros_like(t[0])]
+    v, vo = [torch.randn(16, device=dev)], [torch.zeros(16, device=dev)]
+    p, q, flat = eng.empty(plan.p_elems), torch.randn(plan.q_elems, device=dev), eng.empty(16)
+    plan.timing_enable(True)
+    before = eng.launch_count()
+    plan.set_ptrs(t, o, m, v, vo)
+    plan.pack_vec(flat); plan.p_from_m(p, q); plan.orthogonalize(p, 1); plan.q_from_mt(p, q)
+    plan.finalize(p, q, 1); plan.finish(flat, None, 1)
+    assert eng.launch_count() - before == 7
+    tm = plan.timing_read()
+    assert all(cnt == 1 and ms > 0 for ms, cnt in tm.values())
