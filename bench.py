@@ -43,6 +43,7 @@ def parse():
     ap.add_argument("--skip-cpu-baseline", action="store_true")
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--no-phase-timing", action="store_true")
+    ap.add_argument("--no-clock-probe", action="store_true", help="profiling runs: skip the 1.5 s clock probe")
     return ap.parse_args()
 
 
@@ -276,7 +277,7 @@ def run_b200(args):
     if sampler:
         clocks = sampler.summary(t_wall0, t_wall1)
         clocks["window"] = "timed region"
-    if world > 1 or (clocks is not None and clocks["samples"] < 3):
+    if not args.no_clock_probe and (world > 1 or (clocks is not None and clocks["samples"] < 3)):
         p0 = time.time()
         while time.time() - p0 < 1.5:
             for _ in range(20):

@@ -107,6 +107,9 @@ int psgd_finish(psgd_plan* plan, const float* flat, float* q_mem, float n_worker
 int psgd_timing_enable(psgd_plan* plan, int on);
 /* synchronises the recorded events; ms_sum/count have PSGD_N_PHASES entries; resets */
 int psgd_timing_read(psgd_plan* plan, double* ms_sum, int64_t* count);
+/* development aid: with PSGD_STREAM_DEBUG=1 in the environment at plan creation the streamed P = M Q
+ * kernel records a per-CTA cycle breakdown; this copies it out (8 words per CTA), returns the word count */
+int psgd_debug_read(psgd_plan* plan, uint64_t* out, int max_words);
 /* kernels launched through this library since load (all plans) */
 int64_t psgd_launch_count(void);
 

@@ -39,6 +39,7 @@ SIGNATURES = {
     "psgd_timing_enable": (ctypes.c_int, [vp, ctypes.c_int]),
     "psgd_timing_read": (ctypes.c_int, [vp, c_f64p, c_i64p]),
     "psgd_launch_count": (ctypes.c_int64, []),
+    "psgd_debug_read": (ctypes.c_int, [vp, ctypes.POINTER(ctypes.c_uint64), ctypes.c_int]),
     "psgd_tb_create": (ctypes.c_int, [ctypes.c_int, c_i64p, ctypes.c_int, ctypes.c_int, ctypes.POINTER(vp)]),
     "psgd_tb_destroy": (ctypes.c_int, [vp]),
     "psgd_tb_pack": (ctypes.c_int, [vp, vp, vp, vp]),

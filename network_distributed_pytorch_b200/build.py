@@ -12,7 +12,7 @@ CSRC = os.path.join(PKG, "csrc")
 LIB_DIR = os.path.join(PKG, "lib")
 LIB_PATH = os.path.join(LIB_DIR, "libpsgd_b200.so")
 SOURCES = ["psgd_api.cu"]
-HEADERS = ["psgd_common.cuh", "psgd_kernels.cuh", os.path.join("..", "..", "include", "psgd_b200.h")]
+HEADERS = ["psgd_common.cuh", "psgd_kernels.cuh", "psgd_stream.cuh", os.path.join("..", "..", "include", "psgd_b200.h")]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
@@ -33,6 +33,7 @@ def is_stale():
         return True
     built = os.path.getmtime(LIB_PATH)
     deps = [os.path.join(CSRC, s) for s in SOURCES + HEADERS]
+    deps += [os.path.join(CSRC, f) for f in os.listdir(CSRC) if f.endswith((".cu", ".cuh", ".h"))]
     return any(os.path.getmtime(d) > built for d in deps if os.path.exists(d))
 
 

@@ -11,6 +11,7 @@
 
 #include "../../include/psgd_b200.h"
 #include "psgd_kernels.cuh"
+#include "psgd_stream.cuh"
 
 using namespace psgd;
 
@@ -66,7 +67,24 @@ struct psgd_plan {
   std::vector<long long> q_pre, v_pre;
   long long p_total = 0, q_total = 0, v_total = 0, ws_total = 0;
   int wc_cap = 0;
+  int n_max = 0;
+  std::vector<int> orth_small, orth_tall, orth_generic;  // K2 routing by row count
+  int *d_orth_small = nullptr, *d_orth_tall = nullptr, *d_orth_generic = nullptr;
   size_t smem1 = 0, smem3 = 0, smem4 = 0;
+  // streamed (bulk-copy ring) path for K1 / K4
+  bool stream_ok = false;              // static: smem configuration valid and something qualifies
+  bool stream1_now = false, stream4_now = false;  // per step: every qualifying matrix is 16-byte aligned
+  std::vector<char> eligible;
+  std::vector<StreamTask> tasks1, tasks4;
+  std::vector<int4> tiles1_fb, tiles4_fb;  // direct-load tiles of the matrices that do not qualify
+  StreamTask* d_tasks1 = nullptr;
+  StreamTask* d_tasks4 = nullptr;
+  int* d_counters = nullptr;  // [0..1] K1 task / done counters, [2..3] K4
+  unsigned long long* d_dbg = nullptr;  // PSGD_STREAM_DEBUG: per-CTA cycle breakdown of the last streamed K1
+  int4* d_tiles1_fb = nullptr;
+  int4* d_tiles4_fb = nullptr;
+  int stream_grid = 148, ring_slot_bytes = 0, ring_slots = 0, q_bytes = 0;
+  size_t stream_smem = 0;
   // device tables
   MatDesc* d_mats = nullptr;
   int4* d_tiles1 = nullptr;
@@ -137,6 +155,52 @@ void build_row_tiles(const psgd_plan* p, std::vector<int4>& out, long long targe
     for (long long r0 = 0; r0 < md.n; r0 += t) {
       const int nr = (int)std::min<long long>(t, md.n - r0);
       out.push_back(make_int4(i, (int)r0, nr, 0));
+    }
+  }
+}
+
+// Tasks of the streamed kernels: runs of rows of one qualifying matrix, a whole number of ring units
+// each, with guided-self-scheduling sizes (about remaining / (2 * CTAs) bytes, never below
+// `min_units`).  The largest matrix goes last so that the fine-grained tail of the schedule stays inside
+// one matrix (one Q stage per CTA).
+void build_stream_tasks(const psgd_plan* p, int rows_per_sub, std::vector<StreamTask>& tasks) {
+  tasks.clear();
+  std::vector<int> order;
+  int big = -1;
+  long long total = 0;
+  for (int i = 0; i < p->n_mat; ++i) {
+    if (!p->eligible[i]) continue;
+    total += (long long)p->mats[i].n * p->mats[i].m * 4;
+    if (big < 0 || (long long)p->mats[i].n * p->mats[i].m > (long long)p->mats[big].n * p->mats[big].m) big = i;
+  }
+  for (int i = 0; i < p->n_mat; ++i)
+    if (p->eligible[i] && i != big) order.push_back(i);
+  if (big >= 0) order.push_back(big);
+
+  const long long div = 2LL * p->stream_grid * env_ll("PSGD_GSS_DIV", 1);
+  const long long min_units = std::max<long long>(1, env_ll("PSGD_GSS_MIN_UNITS", 2));
+  long long remaining = total;
+  int rot = 0;
+  for (int i : order) {
+    const MatDesc& md = p->mats[i];
+    const long long row_bytes = (long long)md.m * 4;
+    const int rpu = (int)std::max<long long>(1, p->ring_slot_bytes / row_bytes);
+    const int sub_per_unit = (rpu + rows_per_sub - 1) / rows_per_sub;
+    int row = 0;
+    while (row < md.n) {
+      const long long want = std::max<long long>(1, remaining / std::max<long long>(1, div));
+      long long units = std::max<long long>(min_units, (want + rpu * row_bytes - 1) / (rpu * row_bytes));
+      long long rows = std::min<long long>(units * rpu, md.n - row);
+      StreamTask t;
+      t.mat = i;
+      t.row_begin = row;
+      t.row_end = row + (int)rows;
+      t.rot0 = rot;
+      tasks.push_back(t);
+      const long long nunits = (rows + rpu - 1) / rpu;
+      rot = (int)((rot + nunits * sub_per_unit) % kConsumerWarps);
+      row += (int)rows;
+      remaining -= rows * row_bytes;
     }
   }
 }
@@ -261,6 +325,7 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
     qo += (long long)md.m * md.r;  // reducer.py:98
     p->q_pre[i + 1] = qo;
     mmax = std::max(mmax, md.m);
+    p->n_max = std::max(p->n_max, md.n);
 
     // K3 geometry
     md.cpt = (md.m % 4 == 0 && md.m > 0) ? 4 : 1;
@@ -307,6 +372,57 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
   build_row_tiles(p, p->tiles1, t1_bytes, rows1, true);
   build_row_tiles(p, p->tiles4, t4_bytes, rows4, false);
 
+  {  // streamed path: which matrices qualify, and the shared-memory split between Q stage and ring
+    int smem_optin = 232448, sms = 148;
+    if (device >= 0) {
+      cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
+      cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    }
+    p->stream_grid = (int)env_ll("PSGD_STREAM_GRID", sms);
+    const long long q_cap = env_ll("PSGD_STREAM_QCAP", 100 * 1024);
+    long long slot = env_ll("PSGD_SLOT_BYTES", 48 * 1024);
+    slot = std::max<long long>(1024, (slot / 128) * 128);
+    p->eligible.assign(n_mat, 0);
+    long long qb = 0;
+    if (env_ll("PSGD_STREAM", 1) != 0) {
+      for (int i = 0; i < n_mat; ++i) {
+        const MatDesc& md = p->mats[i];
+        const long long qs = (long long)R * q_pitch(md.m, R) * 4;
+        if (md.n > 0 && md.m > 0 && md.m % 4 == 0 && (long long)md.m * 4 <= slot && qs <= q_cap) {
+          p->eligible[i] = 1;
+          qb = std::max(qb, qs);
+        }
+      }
+    }
+    qb = (qb + 127) & ~127LL;
+    const long long ring = (long long)smem_optin - qb - kStreamSmemExtra - 128;
+    const int slots = (int)std::min<long long>(kMaxSlots, ring / slot);
+    if (qb > 0 && slots >= 2) {
+      p->stream_ok = true;
+      p->ring_slot_bytes = (int)slot;
+      p->ring_slots = slots;
+      p->q_bytes = (int)qb;
+      p->stream_smem = (size_t)qb + (size_t)slots * slot + kStreamSmemExtra;
+      build_stream_tasks(p, rows1, p->tasks1);
+      build_stream_tasks(p, rows4, p->tasks4);
+      for (const int4& t : p->tiles1) if (!p->eligible[t.x]) p->tiles1_fb.push_back(t);
+      for (const int4& t : p->tiles4) if (!p->eligible[t.x]) p->tiles4_fb.push_back(t);
+    } else {
+      p->eligible.assign(n_mat, 0);
+    }
+  }
+
+  {  // K2 routing: register-resident single CTA, register-resident cluster, or generic cluster
+    const int rpt = R <= 8 ? 4 : 2;
+    for (int i = 0; i < n_mat; ++i) {
+      const long long nn = p->mats[i].n;
+      if (nn == 0 || p->mats[i].m == 0) continue;
+      if (R <= 16 && nn <= (long long)kOrthSmallThreads * rpt) p->orth_small.push_back(i);
+      else if (R <= 16 && nn <= (long long)kOrthCluster * kOrthSmallThreads * rpt) p->orth_tall.push_back(i);
+      else p->orth_generic.push_back(i);
+    }
+  }
+
   p->v_pre.assign(n_vec + 1, 0);
   for (int j = 0; j < n_vec; ++j) {
     if (vec_len[j] < 0) {
@@ -330,6 +446,19 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
     rc |= upload(&p->d_tiles3, p->tiles3);
     rc |= upload(&p->d_q_pre, p->q_pre);
     rc |= upload(&p->d_v_pre, p->v_pre);
+    rc |= upload(&p->d_tasks1, p->tasks1);
+    rc |= upload(&p->d_tasks4, p->tasks4);
+    if (!rc && cudaMalloc((void**)&p->d_counters, 4 * sizeof(int)) != cudaSuccess) rc = fail("cudaMalloc(counters) failed");
+    if (!rc && cudaMemset(p->d_counters, 0, 4 * sizeof(int)) != cudaSuccess) rc = fail("cudaMemset(counters) failed");
+    if (!rc && env_ll("PSGD_STREAM_DEBUG", 0)) {
+      const size_t nb = (size_t)p->stream_grid * kDbgWords * sizeof(unsigned long long);
+      if (cudaMalloc((void**)&p->d_dbg, nb) != cudaSuccess || cudaMemset(p->d_dbg, 0, nb) != cudaSuccess) rc = fail("cudaMalloc(dbg) failed");
+    }
+    rc |= upload(&p->d_tiles1_fb, p->tiles1_fb);
+    rc |= upload(&p->d_tiles4_fb, p->tiles4_fb);
+    rc |= upload(&p->d_orth_small, p->orth_small);
+    rc |= upload(&p->d_orth_tall, p->orth_tall);
+    rc |= upload(&p->d_orth_generic, p->orth_generic);
     // ring slot: 5 pointer arrays + flags per matrix, 2 pointer arrays per vector
     size_t sb = (size_t)n_mat * (5 * sizeof(void*) + sizeof(unsigned)) + (size_t)n_vec * 2 * sizeof(void*);
     sb = (sb + 255) & ~(size_t)255;
@@ -360,6 +489,15 @@ int psgd_plan_destroy(psgd_plan* p) {
     cudaFree(p->d_tiles3);
     cudaFree(p->d_q_pre);
     cudaFree(p->d_v_pre);
+    cudaFree(p->d_tasks1);
+    cudaFree(p->d_tasks4);
+    cudaFree(p->d_counters);
+    cudaFree(p->d_dbg);
+    cudaFree(p->d_tiles1_fb);
+    cudaFree(p->d_tiles4_fb);
+    cudaFree(p->d_orth_small);
+    cudaFree(p->d_orth_tall);
+    cudaFree(p->d_orth_generic);
     cudaFree(p->d_ring);
     if (p->h_ring) cudaFreeHost(p->h_ring);
     for (int s = 0; s < kSlots; ++s)
@@ -390,7 +528,7 @@ int psgd_tile_count(const psgd_plan* p, int phase) {
     case PSGD_PHASE_P_FROM_M: return (int)p->tiles1.size();
     case PSGD_PHASE_FINALIZE: return (int)p->tiles4.size();
     case PSGD_PHASE_Q_FROM_MT: return (int)p->tiles3.size();
-    case PSGD_PHASE_ORTH: return p->n_mat * kOrthCluster;
+    case PSGD_PHASE_ORTH: return (int)(p->orth_small.size() + (p->orth_tall.size() + p->orth_generic.size()) * kOrthCluster);
     default: return 0;
   }
 }
@@ -432,7 +570,9 @@ int psgd_set_ptrs(psgd_plan* p, const void* const* mat_in, void* const* mat_out,
   const void** h_vin = (const void**)(h + 5 * L * 8);
   void** h_vout = (void**)(h + 5 * L * 8 + L1 * 8);
   unsigned* h_fl = (unsigned*)(h + 5 * L * 8 + 2 * L1 * 8);
+  const size_t used_bytes = 5 * L * 8 + 2 * L1 * 8 + L * 4;
   p->have_ge = grad && err;
+  bool s1 = p->stream_ok, s4 = p->stream_ok;
   for (size_t i = 0; i < L; ++i) {
     const MatDesc& md = p->mats[i];
     const bool nonempty = md.n && md.m;
@@ -450,12 +590,21 @@ int psgd_set_ptrs(psgd_plan* p, const void* const* mat_in, void* const* mat_out,
     if (m4 && (((uintptr_t)mat_out[i] | (uintptr_t)mat_mem[i]) & 15) == 0) fl |= kFlagOutVec;
     if (p->have_ge && m4 && (((uintptr_t)grad[i] | (uintptr_t)err[i]) & 15) == 0) fl |= kFlagGeVec;
     h_fl[i] = fl;
+    if (p->stream_ok && p->eligible[i]) {
+      if (!(fl & kFlagInVec)) s1 = false;
+      if (!(fl & kFlagInVec) || !(fl & kFlagOutVec)) s4 = false;
+    }
   }
+  p->stream1_now = s1;
+  p->stream4_now = s4;
   for (size_t j = 0; j < L1; ++j) {
     const bool nonempty = p->v_pre[j + 1] > p->v_pre[j];
     if (nonempty && (!vec_in[j] || !vec_out[j])) return fail("psgd_set_ptrs: vector %zu has a null pointer", j);
     h_vin[j] = vec_in[j];
     h_vout[j] = vec_out[j];
+  }
+  if (p->cur >= 0 && memcmp(h, p->h_ring + (size_t)p->cur * p->slot_bytes, used_bytes) == 0) {
+    return 0;  // same addresses as the table already on the device: nothing to upload
   }
   CU(cudaMemcpyAsync(d, h, p->slot_bytes, cudaMemcpyHostToDevice, s));
   CU(cudaEventRecord(p->slot_ev[slot], s));
@@ -496,6 +645,24 @@ int psgd_pack_vec(psgd_plan* p, float* flat, psgd_stream stream) {
     default: return fail("unsupported compile-time rank %d", R_); \
   }
 
+#define DISPATCH_R8(R_, ...)                   \
+  switch (R_) {                                \
+    case 1: { constexpr int RR = 1; __VA_ARGS__; } break;   \
+    case 2: { constexpr int RR = 2; __VA_ARGS__; } break;   \
+    case 4: { constexpr int RR = 4; __VA_ARGS__; } break;   \
+    case 8: { constexpr int RR = 8; __VA_ARGS__; } break;   \
+    default: return fail("unsupported compile-time rank %d", R_); \
+  }
+#define DISPATCH_R16(R_, ...)                  \
+  switch (R_) {                                \
+    case 1: { constexpr int RR = 1; __VA_ARGS__; } break;   \
+    case 2: { constexpr int RR = 2; __VA_ARGS__; } break;   \
+    case 4: { constexpr int RR = 4; __VA_ARGS__; } break;   \
+    case 8: { constexpr int RR = 8; __VA_ARGS__; } break;   \
+    case 16: { constexpr int RR = 16; __VA_ARGS__; } break; \
+    default: return fail("unsupported compile-time rank %d", R_); \
+  }
+
 int psgd_p_from_m(psgd_plan* p, float* p_mem, const float* q_mem, int fuse_add, float q_div, psgd_stream stream) {
   if (need_device(p) || need_ptrs(p)) return 1;
   if (p->tiles1.empty()) return 0;
@@ -507,6 +674,24 @@ int psgd_p_from_m(psgd_plan* p, float* p_mem, const float* q_mem, int fuse_add, 
   const DevPlan dp = dev_plan(p);
   const unsigned grid = (unsigned)p->tiles1.size();
   PhaseScope ts(p, PSGD_PHASE_P_FROM_M, s);
+  if (!fuse_add && p->stream1_now) {
+    StreamPlan sp{p->d_tasks1, p->d_counters, (int)p->tasks1.size(), p->ring_slot_bytes, p->ring_slots, p->q_bytes, p->d_dbg};
+    DISPATCH_R(p->R, {
+      CU(cudaFuncSetAttribute((const void*)k_p_from_m_stream<RR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->stream_smem));
+      k_p_from_m_stream<RR><<<p->stream_grid, kStreamThreads, p->stream_smem, s>>>(dp, p->slot, sp, q_mem, p_mem, q_div);
+    });
+    if (check_launch("k_p_from_m_stream")) return 1;
+    if (!p->tiles1_fb.empty()) {
+      DevPlan fb = dp;
+      fb.tiles1 = p->d_tiles1_fb;
+      DISPATCH_R(p->R, {
+        if (set_smem(k_p_from_m<RR, false>, p->smem1)) return 1;
+        k_p_from_m<RR, false><<<(unsigned)p->tiles1_fb.size(), kThreads, p->smem1, s>>>(fb, p->slot, q_mem, p_mem, q_div);
+      });
+      if (check_launch("k_p_from_m")) return 1;
+    }
+    return 0;
+  }
   DISPATCH_R(p->R, {
     if (fuse_add) {
       if (set_smem(k_p_from_m<RR, true>, p->smem1)) return 1;
@@ -527,21 +712,46 @@ int psgd_orthogonalize(psgd_plan* p, float* p_mem, float n_workers, psgd_stream 
   CU(cudaSetDevice(p->device));
   cudaStream_t s = (cudaStream_t)stream;
   const DevPlan dp = dev_plan(p);
-  cudaLaunchConfig_t cfg{};
-  cfg.gridDim = dim3((unsigned)p->n_mat * kOrthCluster);
-  cfg.blockDim = dim3(kOrthThreads);
-  cfg.dynamicSmemBytes = 0;
-  cfg.stream = s;
-  cudaLaunchAttribute at[1];
-  at[0].id = cudaLaunchAttributeClusterDimension;
-  at[0].val.clusterDim.x = kOrthCluster;
-  at[0].val.clusterDim.y = 1;
-  at[0].val.clusterDim.z = 1;
-  cfg.attrs = at;
-  cfg.numAttrs = 1;
   PhaseScope ts(p, PSGD_PHASE_ORTH, s);
-  DISPATCH_R(p->R, { CU(cudaLaunchKernelEx(&cfg, k_orthogonalize<RR>, dp, p_mem, n_workers)); });
-  return check_launch("k_orthogonalize");
+  // 1. matrices that fit one CTA's registers: one CTA each, block barriers only
+  if (!p->orth_small.empty()) {
+    const unsigned grid = (unsigned)p->orth_small.size();
+    if (p->R <= 8) {
+      DISPATCH_R8(p->R, { k_orth_small<RR, 4><<<grid, kOrthSmallThreads, 0, s>>>(dp, p->d_orth_small, p_mem, n_workers); });
+    } else {
+      k_orth_small<16, 2><<<grid, kOrthSmallThreads, 0, s>>>(dp, p->d_orth_small, p_mem, n_workers);
+    }
+    if (check_launch("k_orth_small")) return 1;
+  }
+  // 2. tall matrices: one thread-block cluster each
+  for (int pass = 0; pass < 2; ++pass) {
+    const std::vector<int>& ids = pass == 0 ? p->orth_tall : p->orth_generic;
+    const int* d_ids = pass == 0 ? p->d_orth_tall : p->d_orth_generic;
+    if (ids.empty()) continue;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3((unsigned)ids.size() * kOrthCluster);
+    cfg.blockDim = dim3(pass == 0 ? kOrthSmallThreads : kOrthThreads);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = s;
+    cudaLaunchAttribute at[1];
+    at[0].id = cudaLaunchAttributeClusterDimension;
+    at[0].val.clusterDim.x = kOrthCluster;
+    at[0].val.clusterDim.y = 1;
+    at[0].val.clusterDim.z = 1;
+    cfg.attrs = at;
+    cfg.numAttrs = 1;
+    if (pass == 0) {
+      if (p->R <= 8) {
+        DISPATCH_R8(p->R, { CU(cudaLaunchKernelEx(&cfg, k_orth_tall<RR, 4>, dp, d_ids, p_mem, n_workers)); });
+      } else {
+        CU(cudaLaunchKernelEx(&cfg, k_orth_tall<16, 2>, dp, d_ids, p_mem, n_workers));
+      }
+    } else {
+      DISPATCH_R(p->R, { CU(cudaLaunchKernelEx(&cfg, k_orthogonalize<RR>, dp, d_ids, p_mem, n_workers)); });
+    }
+    if (check_launch("k_orth_tall")) return 1;
+  }
+  return 0;
 }
 
 int psgd_q_from_mt(psgd_plan* p, const float* p_mem, float* q_mem, void* workspace, psgd_stream stream) {
@@ -581,6 +791,24 @@ int psgd_finalize(psgd_plan* p, const float* p_mem, const float* q_mem, float n_
   const DevPlan dp = dev_plan(p);
   const unsigned grid = (unsigned)p->tiles4.size();
   PhaseScope ts(p, PSGD_PHASE_FINALIZE, s);
+  if (p->stream4_now) {
+    StreamPlan sp{p->d_tasks4, p->d_counters + 2, (int)p->tasks4.size(), p->ring_slot_bytes, p->ring_slots, p->q_bytes, nullptr};
+    DISPATCH_R(p->R, {
+      CU(cudaFuncSetAttribute((const void*)k_finalize_stream<RR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->stream_smem));
+      k_finalize_stream<RR><<<p->stream_grid, kStreamThreads, p->stream_smem, s>>>(dp, p->slot, sp, p_mem, q_mem, n_workers);
+    });
+    if (check_launch("k_finalize_stream")) return 1;
+    if (!p->tiles4_fb.empty()) {
+      DevPlan fb = dp;
+      fb.tiles4 = p->d_tiles4_fb;
+      DISPATCH_R(p->R, {
+        if (set_smem(k_finalize<RR>, p->smem4)) return 1;
+        k_finalize<RR><<<(unsigned)p->tiles4_fb.size(), kThreads, p->smem4, s>>>(fb, p->slot, p_mem, q_mem, n_workers);
+      });
+      if (check_launch("k_finalize")) return 1;
+    }
+    return 0;
+  }
   DISPATCH_R(p->R, {
     if (set_smem(k_finalize<RR>, p->smem4)) return 1;
     k_finalize<RR><<<grid, kThreads, p->smem4, s>>>(dp, p->slot, p_mem, q_mem, n_workers);
@@ -628,6 +856,14 @@ int psgd_timing_read(psgd_plan* p, double* ms_sum, int64_t* count) {
     p->ms_cnt[i] = 0;
   }
   return 0;
+}
+
+int psgd_debug_read(psgd_plan* p, uint64_t* out, int max_words) {
+  if (need_device(p)) return -1;
+  if (!p->d_dbg) return 0;
+  const int n = std::min(max_words, p->stream_grid * kDbgWords);
+  if (cudaMemcpy(out, p->d_dbg, (size_t)n * 8, cudaMemcpyDeviceToHost) != cudaSuccess) return -1;
+  return n;
 }
 
 // ---- stand-alone TensorBuffer packer -----------------------------------------------------

@@ -7,7 +7,8 @@ namespace psgd {
 
 constexpr int kThreads = 256;      // CTA size of the streaming kernels (8 warps)
 constexpr int kWarps = kThreads / 32;
-constexpr int kOrthThreads = 512;  // CTA size of the Gram-Schmidt kernel
+constexpr int kOrthThreads = 512;  // CTA size of the generic (global-memory) Gram-Schmidt kernel
+constexpr int kOrthSmallThreads = 1024;  // CTA size of the register-resident Gram-Schmidt kernels
 constexpr int kOrthCluster = 8;    // CTAs per matrix (one thread-block cluster)
 
 // per-matrix constants, uploaded once per plan

@@ -177,6 +177,7 @@ __device__ __forceinline__ void orth_body(float* __restrict__ P, int n, int r, f
   const int lo = crank * per;
   const int hi = (lo + per < n) ? lo + per : n;
   const bool divide = world != 1.0f;
+  const float inv_world = 1.0f / world;
 
   for (int i = 0; i < r; ++i) {
     float s[R];
@@ -191,7 +192,7 @@ __device__ __forceinline__ void orth_body(float* __restrict__ P, int n, int r, f
         if (j >= i && j < r) {
           v[j] = pr[j];
           if (i == 0 && divide) {
-            v[j] = v[j] / world;
+            v[j] = v[j] * inv_world;
             pr[j] = v[j];
           }
         }
@@ -246,14 +247,14 @@ __device__ __forceinline__ void orth_body(float* __restrict__ P, int n, int r, f
 #pragma unroll
     for (int j = 0; j < R; ++j)
       if (j == i) nrm2 = tot[j];
-    const float denom = sqrtf(nrm2) + 1e-8f;  // eps outside the root, reducer.py:186
+    const float inv = 1.0f / (sqrtf(nrm2) + 1e-8f);  // eps outside the root, reducer.py:186
     float coef[R];
 #pragma unroll
-    for (int j = 0; j < R; ++j) coef[j] = (j > i && j < r) ? tot[j] / denom : 0.f;
+    for (int j = 0; j < R; ++j) coef[j] = (j > i && j < r) ? tot[j] * inv : 0.f;
 
     for (int row = lo + tid; row < hi; row += nthr) {
       float* pr = P + (size_t)row * r;
-      const float vi = pr[i] / denom;
+      const float vi = pr[i] * inv;
       pr[i] = vi;
 #pragma unroll
       for (int j = 0; j < R; ++j)
@@ -263,12 +264,142 @@ __device__ __forceinline__ void orth_body(float* __restrict__ P, int n, int r, f
   }
 }
 
-template <int R>
-__global__ void __launch_bounds__(kOrthThreads)
-k_orthogonalize(DevPlan pl, float* __restrict__ p_mem, float world) {
+// Register-resident variant: every thread keeps its (at most RPT) rows in registers for all r steps,
+// so P is read once and written once and a step costs one block (+ cluster) reduction.  csize == 1
+// runs a whole matrix in one CTA with block barriers only; csize > 1 spreads one tall matrix over a
+// thread-block cluster and exchanges the partials through distributed shared memory.  All sums are
+// formed in a fixed order (xor-shuffle trees, then CTA rank order), so results are deterministic.
+template <int R, int RPT>
+__device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r, float world,
+                                            int crank, int csize) {
+  __shared__ float wsum[32][R];
+  __shared__ float part[2][kOrthCluster][R];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int nthr = blockDim.x, nwarp = nthr >> 5;
+  const int per = (n + csize - 1) / csize;
+  const int lo = crank * per;
+  const int hi = (lo + per < n) ? lo + per : n;
+
+  // IEEE fp32 division costs ~40 instructions; one reciprocal per scale factor and multiplies instead
+  // (exact for power-of-two worker counts, otherwise within 1 ulp of the reference's true division)
+  const bool vec4 = (R == 4) && (r == 4) && ((reinterpret_cast<uintptr_t>(P) & 15) == 0);
+  float v[RPT][R];
+#pragma unroll
+  for (int k = 0; k < RPT; ++k) {
+    const int row = lo + tid + k * nthr;
+    if (vec4) {
+      float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (row < hi) t = *reinterpret_cast<const float4*>(P + (size_t)row * 4);
+      v[k][0] = t.x; v[k][1 % R] = t.y; v[k][2 % R] = t.z; v[k][3 % R] = t.w;
+    } else {
+#pragma unroll
+      for (int j = 0; j < R; ++j) v[k][j] = (row < hi && j < r) ? P[(size_t)row * r + j] : 0.f;
+    }
+  }
+  if (world != 1.0f) {
+    const float inv_world = 1.0f / world;
+#pragma unroll
+    for (int k = 0; k < RPT; ++k)
+#pragma unroll
+      for (int j = 0; j < R; ++j) v[k][j] *= inv_world;
+  }
+
+#pragma unroll
+  for (int i = 0; i < R; ++i) {
+    if (i < r) {  // uniform over the CTA / cluster
+      float s[R];
+#pragma unroll
+      for (int j = 0; j < R; ++j) s[j] = 0.f;
+#pragma unroll
+      for (int k = 0; k < RPT; ++k)
+#pragma unroll
+        for (int j = i; j < R; ++j) s[j] = fmaf(v[k][i], v[k][j], s[j]);
+#pragma unroll
+      for (int j = i; j < R; ++j) {
+        if (j < r) {
+          const float w = warp_sum(s[j]);
+          if (lane == 0) wsum[warp][j] = w;
+        }
+      }
+      __syncthreads();
+      const int par = i & 1;
+      if (warp == 0) {
+#pragma unroll
+        for (int j = i; j < R; ++j) {
+          if (j < r) {
+            const float t = warp_sum(lane < nwarp ? wsum[lane][j] : 0.f);
+            if (csize > 1) {
+              if (lane < csize) {
+                float* remote = cg::this_cluster().map_shared_rank(&part[0][0][0], lane);
+                remote[(par * kOrthCluster + crank) * R + j] = t;
+              }
+            } else if (lane == 0) {
+              part[par][0][j] = t;
+            }
+          }
+        }
+      }
+      if (csize > 1) cg::this_cluster().sync(); else __syncthreads();
+      float tot[R];
+#pragma unroll
+      for (int j = i; j < R; ++j) {
+        tot[j] = 0.f;
+        if (j < r)
+          for (int c = 0; c < csize; ++c) tot[j] += part[par][c][j];
+      }
+      const float inv = 1.0f / (sqrtf(tot[i]) + 1e-8f);  // eps outside the root, reducer.py:186
+      float coef[R];
+#pragma unroll
+      for (int j = i + 1; j < R; ++j) coef[j] = tot[j] * inv;
+#pragma unroll
+      for (int k = 0; k < RPT; ++k) {
+        const float vi = v[k][i] * inv;
+        v[k][i] = vi;
+#pragma unroll
+        for (int j = i + 1; j < R; ++j)
+          if (j < r) v[k][j] = fmaf(-coef[j], vi, v[k][j]);
+      }
+    }
+  }
+#pragma unroll
+  for (int k = 0; k < RPT; ++k) {
+    const int row = lo + tid + k * nthr;
+    if (row < hi) {
+      if (vec4) {
+        *reinterpret_cast<float4*>(P + (size_t)row * 4) = make_float4(v[k][0], v[k][1 % R], v[k][2 % R], v[k][3 % R]);
+      } else {
+#pragma unroll
+        for (int j = 0; j < R; ++j)
+          if (j < r) P[(size_t)row * r + j] = v[k][j];
+      }
+    }
+  }
+}
+
+// one CTA per "small" matrix (n <= blockDim * RPT)
+template <int R, int RPT>
+__global__ void __launch_bounds__(kOrthSmallThreads)
+k_orth_small(DevPlan pl, const int* __restrict__ ids, float* __restrict__ p_mem, float world) {
+  const MatDesc md = pl.mats[ids[blockIdx.x]];
+  orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, 0, 1);
+}
+
+// one cluster per "tall" matrix (n <= cluster * blockDim * RPT)
+template <int R, int RPT>
+__global__ void __launch_bounds__(kOrthSmallThreads)
+k_orth_tall(DevPlan pl, const int* __restrict__ ids, float* __restrict__ p_mem, float world) {
   cg::cluster_group cluster = cg::this_cluster();
   const int csize = (int)cluster.num_blocks();
-  const int mat = blockIdx.x / csize;
+  const MatDesc md = pl.mats[ids[blockIdx.x / csize]];
+  orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, (int)cluster.block_rank(), csize);
+}
+
+template <int R>
+__global__ void __launch_bounds__(kOrthThreads)
+k_orthogonalize(DevPlan pl, const int* __restrict__ ids, float* __restrict__ p_mem, float world) {
+  cg::cluster_group cluster = cg::this_cluster();
+  const int csize = (int)cluster.num_blocks();
+  const int mat = ids[blockIdx.x / csize];
   const MatDesc md = pl.mats[mat];
   orth_body<R>(p_mem + md.p_off, md.n, md.r, world, (int)cluster.block_rank(), csize, true);
 }

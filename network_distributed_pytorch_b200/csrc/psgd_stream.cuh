@@ -1,0 +1,467 @@
+// Persistent, warp-specialised streaming kernels for the two row-streaming phases (K1: P = M Q and
+// K4+K5: out = P Q^T, mem = M - out).  One CTA per SM; one producer thread keeps a ring of shared-
+// memory slots full with bulk asynchronous copies (cp.async.bulk, the 1-D TMA path) signalled through
+// mbarriers; eight consumer warps take sub-spans of ROWS rows each, read M and the transposed Q copy
+// from shared memory and run the rank-r FMAs.  Bytes in flight per SM are set by the ring (~150 KB)
+// instead of by registers, which is what lets a read stream approach the HBM limit.
+//
+// Everything the consumers need arrives through the ring, in order: when the producer moves to a new
+// matrix it first sends that matrix' Q (raw, row-major) as ring units, the consumers transpose it from
+// the slot into the Q stage (shared -> shared), then the M units follow.  No consumer ever waits on a
+// global load in steady state.  Work is handed out dynamically (guided self-scheduling over a global
+// task counter): with equal static shares the SMs finish up to 40 % apart.
+//
+// Matrices that do not qualify (m % 4 != 0, unaligned base, a row that does not fit a slot, Q too large
+// for the stage) are left to the direct-load kernels in psgd_kernels.cuh.
+#pragma once
+#include "psgd_common.cuh"
+
+namespace psgd {
+
+constexpr int kConsumerWarps = 8;
+constexpr int kStreamThreads = (kConsumerWarps + 1) * 32;  // + 1 producer warp
+constexpr int kMaxSlots = 8;
+constexpr int kMatCache = 256;  // matrices whose {base, q, m, r} are cached in shared memory
+
+// A task is a run of rows of ONE matrix, cut by the producer into units of at most one slot.
+struct StreamTask {
+  int mat, row_begin, row_end, rot0;
+};
+
+struct StreamPlan {
+  const StreamTask* tasks;
+  int* counters;         // [0] next task, [1] CTAs finished (the last one re-arms both for the next launch)
+  int n_tasks;
+  int slot_bytes;        // bytes per ring slot (multiple of 128)
+  int n_slots;
+  int q_bytes;           // bytes reserved for the transposed Q stage
+  unsigned long long* dbg;  // optional per-CTA cycle breakdown (PSGD_STREAM_DEBUG), else nullptr
+};
+constexpr int kDbgWords = 8;  // per CTA: t0, t1 (ns), cycles: desc wait, data wait, Q units, total, units, switches
+
+// what travels with a slot: an M unit {mat, row0, nrows > 0, rot}, a Q unit {mat, j0, -count, flags},
+// or the end marker {mat < 0}
+constexpr int kQFlagBulk = 1 << 16;  // Q unit: data was bulk-copied into the slot (else: fetch from global)
+
+__device__ __forceinline__ unsigned long long gtime_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+  return t;
+}
+
+// ---- PTX wrappers ---------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t smem_u32(const void* p) {
+  return static_cast<uint32_t>(__cvta_generic_to_shared(p));
+}
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_fence_init() {
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_n(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "WAIT_%=:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra DONE_%=;\n"
+      "bra WAIT_%=;\n"
+      "DONE_%=:\n"
+      "}\n" ::"r"(smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+// global -> shared bulk copy (bytes % 16 == 0, both addresses 16-byte aligned), completion on `bar`
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void consumer_sync() {  // named barrier over the consumer warps only
+  asm volatile("bar.sync 1, %0;" ::"n"(kConsumerWarps * 32) : "memory");
+}
+
+template <int R> struct RowsS1 { static constexpr int v = (R <= 2) ? 8 : (R <= 8) ? 4 : (R == 16) ? 2 : 1; };
+template <int R> struct RowsS4 { static constexpr int v = (R <= 8) ? 4 : (R == 16) ? 2 : 1; };
+
+// shared memory map: [Q stage | ring slots | full, empty, desc barriers | descriptor per slot | matrix cache]
+struct StreamSmem {
+  float* qs;
+  unsigned char* ring;
+  uint64_t* full;   // data of the slot has landed (tx bytes)
+  uint64_t* empty;  // all consumer warps are done with the slot
+  uint64_t* desc;   // the slot's descriptor is published (well before its data lands)
+  volatile int4* slot_desc;
+  struct MatInfo { const float* base; const float* q; int m; int r; long long pad; };
+  MatInfo* matinfo;
+};
+constexpr int kStreamSmemExtra = 3 * kMaxSlots * 8 + kMaxSlots * 16 + kMatCache * 32;
+
+__device__ __forceinline__ StreamSmem carve(unsigned char* base, const StreamPlan& sp) {
+  StreamSmem s;
+  s.qs = reinterpret_cast<float*>(base);
+  s.ring = base + sp.q_bytes;
+  s.full = reinterpret_cast<uint64_t*>(base + sp.q_bytes + (size_t)sp.n_slots * sp.slot_bytes);
+  s.empty = s.full + kMaxSlots;
+  s.desc = s.empty + kMaxSlots;
+  s.slot_desc = reinterpret_cast<volatile int4*>(s.desc + kMaxSlots);
+  s.matinfo = reinterpret_cast<StreamSmem::MatInfo*>(const_cast<int4*>(s.slot_desc) + kMaxSlots);
+  return s;
+}
+
+__device__ __forceinline__ StreamSmem::MatInfo mat_info(const DevPlan& pl, const PtrSlot& ps, const StreamSmem& sm,
+                                                        const float* q_mem, int mat) {
+  if (mat < kMatCache) return sm.matinfo[mat];
+  StreamSmem::MatInfo mi;
+  const MatDesc md = pl.mats[mat];
+  mi.base = ps.in[mat];
+  mi.q = q_mem + md.q_off;
+  mi.m = md.m;
+  mi.r = md.r;
+  mi.pad = 0;
+  return mi;
+}
+
+// common prologue: barriers + matrix cache
+__device__ __forceinline__ void stream_setup(const DevPlan& pl, const PtrSlot& ps, const StreamPlan& sp,
+                                             const StreamSmem& sm, const float* q_mem) {
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < sp.n_slots; ++s) {
+      mbar_init(&sm.full[s], 1);
+      mbar_init(&sm.empty[s], kConsumerWarps);
+      mbar_init(&sm.desc[s], 1);
+    }
+    mbar_fence_init();
+  }
+  for (int i = threadIdx.x; i < pl.n_mat && i < kMatCache; i += blockDim.x) {
+    const MatDesc md = pl.mats[i];
+    sm.matinfo[i].base = ps.in[i];
+    sm.matinfo[i].q = q_mem + md.q_off;
+    sm.matinfo[i].m = md.m;
+    sm.matinfo[i].r = md.r;
+  }
+  __syncthreads();
+}
+
+// The producer: one thread takes tasks from the global counter, cuts them into units and refills slots
+// as the consumers release them.  Nothing on its per-unit path touches global memory: the task after
+// the current one is requested while the current one streams.
+template <int ROWS>
+__device__ __forceinline__ void stream_producer(const DevPlan& pl, const PtrSlot& ps, const StreamPlan& sp,
+                                                const StreamSmem& sm, const float* q_mem) {
+  int it = 0;
+  int prev_mat = -1;
+  int t = atomicAdd(&sp.counters[0], 1);
+  StreamTask task = sp.tasks[t < sp.n_tasks ? t : 0];
+  while (t < sp.n_tasks) {
+    const int t_next = atomicAdd(&sp.counters[0], 1);  // in flight while this task streams
+    const StreamSmem::MatInfo mi = mat_info(pl, ps, sm, q_mem, task.mat);
+    const int m = mi.m;
+    if (task.mat != prev_mat) {  // new matrix: its Q goes first
+      const bool bulk = (reinterpret_cast<uintptr_t>(mi.q) & 15) == 0;
+      const int qrows = max(4, (sp.slot_bytes / (mi.r * 4)) & ~3);
+      for (int j0 = 0; j0 < m; j0 += qrows, ++it) {
+        const int cnt = min(qrows, m - j0);
+        const int slot = it % sp.n_slots;
+        const uint32_t phase = (uint32_t)(it / sp.n_slots) & 1u;
+        mbar_wait(&sm.empty[slot], phase ^ 1u);
+        sm.slot_desc[slot].x = task.mat; sm.slot_desc[slot].y = j0;
+        sm.slot_desc[slot].z = -cnt; sm.slot_desc[slot].w = bulk ? kQFlagBulk : 0;
+        mbar_arrive(&sm.desc[slot]);
+        if (bulk) {
+          const uint32_t bytes = (uint32_t)cnt * (uint32_t)mi.r * 4u;
+          mbar_arrive_expect_tx(&sm.full[slot], bytes);
+          bulk_g2s(sm.ring + (size_t)slot * sp.slot_bytes, mi.q + (size_t)j0 * mi.r, bytes, &sm.full[slot]);
+        } else {
+          mbar_arrive(&sm.full[slot]);
+        }
+      }
+      prev_mat = task.mat;
+    }
+    const int rpu = max(1, sp.slot_bytes / (m * 4));
+    const int sub_per_unit = (rpu + ROWS - 1) / ROWS;
+    int rot = task.rot0;
+    for (int row0 = task.row_begin; row0 < task.row_end; row0 += rpu, ++it) {
+      const int nrows = min(rpu, task.row_end - row0);
+      const int slot = it % sp.n_slots;
+      const uint32_t phase = (uint32_t)(it / sp.n_slots) & 1u;
+      mbar_wait(&sm.empty[slot], phase ^ 1u);  // passes at once on the first lap
+      const uint32_t bytes = (uint32_t)nrows * (uint32_t)m * 4u;
+      sm.slot_desc[slot].x = task.mat; sm.slot_desc[slot].y = row0;
+      sm.slot_desc[slot].z = nrows; sm.slot_desc[slot].w = rot;
+      mbar_arrive(&sm.desc[slot]);
+      mbar_arrive_expect_tx(&sm.full[slot], bytes);
+      bulk_g2s(sm.ring + (size_t)slot * sp.slot_bytes, mi.base + (size_t)row0 * m, bytes, &sm.full[slot]);
+      rot = (rot + sub_per_unit) % kConsumerWarps;
+    }
+    t = t_next;
+    if (t < sp.n_tasks) task = sp.tasks[t];  // one round trip, covered by the slots already in flight
+  }
+  {  // end marker
+    const int slot = it % sp.n_slots;
+    const uint32_t phase = (uint32_t)(it / sp.n_slots) & 1u;
+    mbar_wait(&sm.empty[slot], phase ^ 1u);
+    sm.slot_desc[slot].x = -1;
+    mbar_arrive(&sm.desc[slot]);
+  }
+  // the last CTA to get here re-arms the counters, so the next launch needs no memset
+  __threadfence();
+  if (atomicAdd(&sp.counters[1], 1) == (int)gridDim.x - 1) {
+    sp.counters[0] = 0;
+    sp.counters[1] = 0;
+    __threadfence();
+  }
+}
+
+// Consumers, Q unit: rows [j0, j0 + cnt) of the row-major m x r matrix Q -> transposed stage
+// Qs[c * pitch + j] = Q[j * r + c] / div, rows c in [r, R) zeroed.  Called by all consumer threads.
+template <int R>
+__device__ __forceinline__ void consume_q_unit(float* Qs, const float* slot, const float* __restrict__ qglobal,
+                                               bool bulk, int j0, int cnt, int m, int r, int pitch, float div) {
+  constexpr int NT = kConsumerWarps * 32;
+  const float* src = bulk ? slot : qglobal + (size_t)j0 * r;
+  if (bulk && r == R && (R % 4) == 0) {  // one row of Q per thread and step: 128-bit reads, conflict-free writes
+    for (int j = threadIdx.x; j < cnt; j += NT) {
+#pragma unroll
+      for (int c4 = 0; c4 < R; c4 += 4) {
+        float4 v = *reinterpret_cast<const float4*>(src + (size_t)j * R + c4);
+        if (div != 1.0f) { v.x = v.x / div; v.y = v.y / div; v.z = v.z / div; v.w = v.w / div; }
+        Qs[(c4 + 0) * pitch + j0 + j] = v.x;
+        Qs[(c4 + 1) % R * pitch + j0 + j] = v.y;
+        Qs[(c4 + 2) % R * pitch + j0 + j] = v.z;
+        Qs[(c4 + 3) % R * pitch + j0 + j] = v.w;
+      }
+    }
+  } else {
+    for (int j = threadIdx.x; j < cnt; j += NT) {
+      for (int c = 0; c < r; ++c) {
+        float v = bulk ? src[(size_t)j * r + c] : __ldg(src + (size_t)j * r + c);
+        if (div != 1.0f) v = v / div;
+        Qs[c * pitch + j0 + j] = v;
+      }
+    }
+  }
+  if (r < R && j0 == 0) {
+    const int zt = (R - r) * m;
+    for (int e = threadIdx.x; e < zt; e += NT) Qs[(r + e / m) * pitch + (e % m)] = 0.f;
+  }
+}
+
+// =======================================================================================
+// K1 (streamed):  P = M Q
+// =======================================================================================
+template <int R>
+__global__ void __launch_bounds__(kStreamThreads, 1)
+k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict__ q_mem, float* __restrict__ p_mem,
+                  float q_div) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  constexpr int ROWS = RowsS1<R>::v;
+  constexpr int NV = ROWS * R;
+  const StreamSmem sm = carve(smem_raw, sp);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  stream_setup(pl, ps, sp, sm, q_mem);
+
+  if (warp == kConsumerWarps) {
+    if (lane == 0) stream_producer<ROWS>(pl, ps, sp, sm, q_mem);
+    return;
+  }
+
+  int cur_mat = -1, m = 0, r = 0, pitch = 0;
+  float* P = nullptr;
+  const bool dbg = sp.dbg != nullptr && threadIdx.x == 0;
+  unsigned long long d_t0 = 0, d_desc = 0, d_data = 0, d_q = 0, d_units = 0, d_sw = 0;
+  long long c0 = 0, c_begin = 0;
+  if (dbg) { d_t0 = gtime_ns(); c_begin = clock64(); }
+  for (int it = 0;; ++it) {
+    const int slot = it % sp.n_slots;
+    const uint32_t phase = (uint32_t)(it / sp.n_slots) & 1u;
+    if (dbg) c0 = clock64();
+    mbar_wait(&sm.desc[slot], phase);
+    if (dbg) d_desc += clock64() - c0;
+    const int u_mat = sm.slot_desc[slot].x, u_a = sm.slot_desc[slot].y;
+    const int u_n = sm.slot_desc[slot].z, u_w = sm.slot_desc[slot].w;
+    if (u_mat < 0) break;
+    const float* base = reinterpret_cast<const float*>(sm.ring + (size_t)slot * sp.slot_bytes);
+    if (u_n < 0) {  // Q unit (uniform over the consumer warps: every warp visits every unit)
+      if (dbg) c0 = clock64();
+      const StreamSmem::MatInfo mi = mat_info(pl, ps, sm, q_mem, u_mat);
+      if (u_mat != cur_mat) {
+        P = p_mem + pl.mats[u_mat].p_off;  // in flight while the Q data lands
+        m = mi.m; r = mi.r; pitch = q_pitch(m, R);
+        cur_mat = u_mat;
+        consumer_sync();  // everyone is done with the previous matrix' Q
+      }
+      mbar_wait(&sm.full[slot], phase);
+      consume_q_unit<R>(sm.qs, base, mi.q, (u_w & kQFlagBulk) != 0, u_a, -u_n, m, r, pitch, q_div);
+      consumer_sync();
+      if (lane == 0) mbar_arrive(&sm.empty[slot]);
+      if (dbg) { d_q += clock64() - c0; ++d_sw; }
+      continue;
+    }
+    const int nsub = (u_n + ROWS - 1) / ROWS;
+    // sub-span j of this unit belongs to warp (rot + j) % kConsumerWarps; a warp without a sub-span skips
+    // the unit altogether (its share of the slot's release count is handed in by the j == 0 warp), so the
+    // release of a slot depends only on the warps that actually read it
+    const int j0 = (warp - u_w % kConsumerWarps + kConsumerWarps) % kConsumerWarps;
+    if (j0 >= nsub) continue;
+    if (dbg) c0 = clock64();
+    mbar_wait(&sm.full[slot], phase);
+    if (dbg) { d_data += clock64() - c0; ++d_units; }
+    const int kmax = m >> 2;
+    for (int j = j0; j < nsub; j += kConsumerWarps) {
+      const int rbase = j * ROWS;
+      const int nr = (u_n - rbase < ROWS) ? (u_n - rbase) : ROWS;
+      const float* rowp[ROWS];
+#pragma unroll
+      for (int a = 0; a < ROWS; ++a) rowp[a] = base + (size_t)(rbase + (a < nr ? a : nr - 1)) * m;
+      float acc[ROWS][R];
+#pragma unroll
+      for (int a = 0; a < ROWS; ++a)
+#pragma unroll
+        for (int c = 0; c < R; ++c) acc[a][c] = 0.f;
+#pragma unroll 2
+      for (int k = lane; k < kmax; k += 32) {
+        float4 x[ROWS];
+#pragma unroll
+        for (int a = 0; a < ROWS; ++a) x[a] = *reinterpret_cast<const float4*>(rowp[a] + 4 * k);
+#pragma unroll
+        for (int c = 0; c < R; ++c) {
+          const float4 q = *reinterpret_cast<const float4*>(sm.qs + c * pitch + 4 * k);
+#pragma unroll
+          for (int a = 0; a < ROWS; ++a) {
+            acc[a][c] = fmaf(x[a].x, q.x, acc[a][c]);
+            acc[a][c] = fmaf(x[a].y, q.y, acc[a][c]);
+            acc[a][c] = fmaf(x[a].z, q.z, acc[a][c]);
+            acc[a][c] = fmaf(x[a].w, q.w, acc[a][c]);
+          }
+        }
+      }
+      float flat[NV];
+#pragma unroll
+      for (int a = 0; a < ROWS; ++a)
+#pragma unroll
+        for (int c = 0; c < R; ++c) flat[a * R + c] = acc[a][c];
+      const float tot = warp_fold<NV>(flat, lane);
+      constexpr int LPV = 32 / NV;
+      if ((lane % LPV) == 0) {
+        const int idx = lane / LPV;
+        const int a = idx / R, c = idx % R;
+        if (a < nr && c < r) P[(size_t)(u_a + rbase + a) * r + c] = tot;
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive_n(&sm.empty[slot], (j0 == 0 && nsub < kConsumerWarps) ? 1 + kConsumerWarps - nsub : 1);
+  }
+  if (dbg) {
+    unsigned long long* o = sp.dbg + (size_t)blockIdx.x * kDbgWords;
+    o[0] = d_t0; o[1] = gtime_ns(); o[2] = d_desc; o[3] = d_data; o[4] = d_q;
+    o[5] = (unsigned long long)(clock64() - c_begin); o[6] = d_units; o[7] = d_sw;
+  }
+}
+
+// =======================================================================================
+// K4 + K5 (streamed):  out = P (Q / n_workers)^T ; mem = M - out
+// =======================================================================================
+template <int R>
+__global__ void __launch_bounds__(kStreamThreads, 1)
+k_finalize_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict__ p_mem,
+                  const float* __restrict__ q_mem, float world) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  constexpr int ROWS = RowsS4<R>::v;
+  const StreamSmem sm = carve(smem_raw, sp);
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  stream_setup(pl, ps, sp, sm, q_mem);
+
+  if (warp == kConsumerWarps) {
+    if (lane == 0) stream_producer<ROWS>(pl, ps, sp, sm, q_mem);
+    return;
+  }
+
+  int cur_mat = -1, m = 0, r = 0, pitch = 0;
+  const float* P = nullptr;
+  float* Out = nullptr;
+  float* Mem = nullptr;
+  for (int it = 0;; ++it) {
+    const int slot = it % sp.n_slots;
+    const uint32_t phase = (uint32_t)(it / sp.n_slots) & 1u;
+    mbar_wait(&sm.desc[slot], phase);
+    const int u_mat = sm.slot_desc[slot].x, u_a = sm.slot_desc[slot].y;
+    const int u_n = sm.slot_desc[slot].z, u_w = sm.slot_desc[slot].w;
+    if (u_mat < 0) break;
+    const float* base = reinterpret_cast<const float*>(sm.ring + (size_t)slot * sp.slot_bytes);
+    if (u_n < 0) {  // Q unit
+      const StreamSmem::MatInfo mi = mat_info(pl, ps, sm, q_mem, u_mat);
+      if (u_mat != cur_mat) {
+        P = p_mem + pl.mats[u_mat].p_off;  // these three loads are in flight while the Q data lands
+        Out = ps.out[u_mat];
+        Mem = ps.mem[u_mat];
+        m = mi.m; r = mi.r; pitch = q_pitch(m, R);
+        cur_mat = u_mat;
+        consumer_sync();
+      }
+      mbar_wait(&sm.full[slot], phase);
+      consume_q_unit<R>(sm.qs, base, mi.q, (u_w & kQFlagBulk) != 0, u_a, -u_n, m, r, pitch, world);
+      consumer_sync();
+      if (lane == 0) mbar_arrive(&sm.empty[slot]);
+      continue;
+    }
+    const int nsub = (u_n + ROWS - 1) / ROWS;
+    const int j0 = (warp - u_w % kConsumerWarps + kConsumerWarps) % kConsumerWarps;
+    if (j0 >= nsub) continue;  // see k_p_from_m_stream
+    const int kmax = m >> 2;
+    bool landed = false;
+    for (int j = j0; j < nsub; j += kConsumerWarps) {
+      const int rbase = j * ROWS;
+      const int nr = (u_n - rbase < ROWS) ? (u_n - rbase) : ROWS;
+      float p[ROWS][R];  // the P rows do not live in the slot: request them before waiting for M
+#pragma unroll
+      for (int a = 0; a < ROWS; ++a) {
+        const int rr = u_a + rbase + (a < nr ? a : nr - 1);
+#pragma unroll
+        for (int c = 0; c < R; ++c) p[a][c] = (c < r) ? __ldg(P + (size_t)rr * r + c) : 0.f;
+      }
+      if (!landed) {
+        mbar_wait(&sm.full[slot], phase);
+        landed = true;
+      }
+#pragma unroll 2
+      for (int k = lane; k < kmax; k += 32) {
+        float4 q[R];
+#pragma unroll
+        for (int c = 0; c < R; ++c) q[c] = *reinterpret_cast<const float4*>(sm.qs + c * pitch + 4 * k);
+#pragma unroll
+        for (int a = 0; a < ROWS; ++a) {
+          if (a < nr) {
+            const float4 x = *reinterpret_cast<const float4*>(base + (size_t)(rbase + a) * m + 4 * k);
+            float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll
+            for (int c = 0; c < R; ++c) {
+              o.x = fmaf(p[a][c], q[c].x, o.x);
+              o.y = fmaf(p[a][c], q[c].y, o.y);
+              o.z = fmaf(p[a][c], q[c].z, o.z);
+              o.w = fmaf(p[a][c], q[c].w, o.w);
+            }
+            const size_t g = (size_t)(u_a + rbase + a) * m + 4 * k;
+            st_stream4(Out + g, o);
+            st_stream4(Mem + g, make_float4(x.x - o.x, x.y - o.y, x.z - o.z, x.w - o.w));
+          }
+        }
+      }
+    }
+    __syncwarp();
+    if (lane == 0) mbar_arrive_n(&sm.empty[slot], (j0 == 0 && nsub < kConsumerWarps) ? 1 + kConsumerWarps - nsub : 1);
+  }
+}
+
+}  // namespace psgd

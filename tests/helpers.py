@@ -54,3 +54,23 @@ def per_tensor_rel_err(flat_a, flat_b, shapes):
         out.append(rel_err(flat_a[off : off + k], flat_b[off : off + k]))
         off += k
     return out
+
+
+def per_tensor_mem_err(flat_a, flat_b, flat_in, shapes):
+    """Error of memory_out per tensor.  memory = M - P Q^T, so its absolute error is that of the
+    decompressed gradient; when the rank-r approximation is exact (r = min(n, m), e.g. a (2, 768)
+    classifier at rank 4) the reference's memory is itself pure rounding noise of size ~1e-7 |M| and a
+    ratio of two noises says nothing.  Those tensors (|mem_ref| < 1e-3 |M|) are measured against |M|,
+    all others against |mem_ref| as usual."""
+    out, off = [], 0
+    for s in shapes:
+        k = int(np.prod(s)) if len(s) else 1
+        a = np.asarray(flat_a[off : off + k], np.float64)
+        b = np.asarray(flat_b[off : off + k], np.float64)
+        m = np.asarray(flat_in[off : off + k], np.float64)
+        nb, nm = np.linalg.norm(b), np.linalg.norm(m)
+        den = nm if nb < 1e-3 * nm else nb
+        num = np.linalg.norm(a - b)
+        out.append(0.0 if num == 0 else num / max(den, 1e-300))
+        off += k
+    return out
