@@ -38,7 +38,7 @@ def parse():
     ap.add_argument("--rank", type=int, default=4, help="PowerSGD compression rank")
     ap.add_argument("--no-reuse-query", action="store_true")
     ap.add_argument("--extra-power-iterations", type=int, default=0)
-    ap.add_argument("--e2e-steps", type=int, default=5)
+    ap.add_argument("--e2e-steps", type=int, default=10)
     ap.add_argument("--cpu-reps", type=int, default=5)
     ap.add_argument("--skip-cpu-baseline", action="store_true")
     ap.add_argument("--skip-e2e", action="store_true")
@@ -244,7 +244,9 @@ def run_b200(args):
         red.reduce(gin, gout, mem)
     plan = next(iter(red._plans.values()))
     if not args.no_phase_timing:
-        plan.timing_enable(True)
+        # only the dominant kernel is bracketed inside the timed region: every bracketed phase costs a
+        # few microseconds of stream time (all seven together: ~13 % of the step)
+        plan.timing_enable(["finalize"])
         plan.timing_read()
 
     sampler = ClockSampler(local) if rank == 0 else None
@@ -258,8 +260,10 @@ def run_b200(args):
     launches0 = lib.psgd_launch_count()
     t_wall0 = time.time()
     ev0.record()
+    h0 = time.perf_counter()
     for _ in range(K):
         red.reduce(gin, gout, mem)
+    host_us = (time.perf_counter() - h0) / K * 1e6  # host time to issue one step (no sync inside)
     ev1.record()
     barrier()
     t_wall1 = time.time()
@@ -267,6 +271,14 @@ def run_b200(args):
     ms = ev0.elapsed_time(ev1)
     phases = plan.timing_read() if not args.no_phase_timing else {}
     plan.timing_enable(False)
+    all_phases = {}
+    if not args.no_phase_timing:  # diagnostic breakdown, outside the timed region
+        plan.timing_enable(True)
+        for _ in range(min(K, 20)):
+            red.reduce(gin, gout, mem)
+        torch.cuda.synchronize()
+        all_phases = plan.timing_read()
+        plan.timing_enable(False)
     tmax = torch.tensor([ms], device=dev)
     if world > 1:
         dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
@@ -290,23 +302,50 @@ def run_b200(args):
     barrier()
 
     # ---- e2e: gradients start in pinned host memory, grad_out is read back ------------------------
+    # Three streams and two device buffer sets: the H2D copy of step k+1 and the D2H copy of step k-1 run on
+    # the two copy engines while step k reduces, exactly as a host-resident caller would pipeline the
+    # public reduce() call.  Every step still copies all of its inputs in and its result out.
     e2e = None
     if not args.skip_e2e:
         host_in = torch.empty(total, dtype=torch.float32, pin_memory=True)
         host_out = torch.empty(total, dtype=torch.float32, pin_memory=True)
         host_in.copy_(in_flat)
-        E = max(1, args.e2e_steps)
-        for _ in range(2):
-            in_flat.copy_(host_in, non_blocking=True)
-            red.reduce(gin, gout, mem)
-            host_out.copy_(out_flat, non_blocking=True)
+        ins = [in_flat, torch.empty_like(in_flat)]
+        outs = [out_flat, torch.empty_like(out_flat)]
+        gins = [gin, padded_views(ins[1], shapes)]
+        gouts = [gout, padded_views(outs[1], shapes)]
+        s_h2d, s_d2h = torch.cuda.Stream(dev), torch.cuda.Stream(dev)
+        s_main = torch.cuda.current_stream(dev)
+        ev_in = [torch.cuda.Event() for _ in range(2)]     # H2D of buffer b finished
+        ev_red = [torch.cuda.Event() for _ in range(2)]    # reduce() on buffer b finished
+        ev_out = [torch.cuda.Event() for _ in range(2)]    # D2H of buffer b finished
+
+        def e2e_steps(n):
+            for k in range(n):
+                b = k & 1
+                with torch.cuda.stream(s_h2d):
+                    if k >= 2:
+                        s_h2d.wait_event(ev_red[b])        # reduce k-2 no longer reads in[b]
+                    ins[b].copy_(host_in, non_blocking=True)   # H2D of this step's gradients
+                    ev_in[b].record(s_h2d)
+                s_main.wait_event(ev_in[b])
+                if k >= 2:
+                    s_main.wait_event(ev_out[b])           # D2H k-2 no longer reads out[b]
+                red.reduce(gins[b], gouts[b], mem)         # public API call
+                ev_red[b].record(s_main)
+                with torch.cuda.stream(s_d2h):
+                    s_d2h.wait_event(ev_red[b])
+                    host_out.copy_(outs[b], non_blocking=True)  # D2H of the step's result (grad_out)
+                    ev_out[b].record(s_d2h)
+            s_main.wait_stream(s_d2h)
+            s_main.wait_stream(s_h2d)
+
+        E = max(2, args.e2e_steps)
+        e2e_steps(2)
         barrier()
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         e0.record()
-        for _ in range(E):
-            in_flat.copy_(host_in, non_blocking=True)       # H2D of this step's gradients
-            red.reduce(gin, gout, mem)                      # public API call
-            host_out.copy_(out_flat, non_blocking=True)     # D2H of the step's result (grad_out)
+        e2e_steps(E)
         e1.record()
         barrier()
         ems = torch.tensor([e0.elapsed_time(e1)], device=dev)
@@ -315,7 +354,8 @@ def run_b200(args):
         ems = float(ems.item()) / E
         e2e = {"value": world * st["grad_bytes"] / (ems * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": ems,
                "steps": E, "h2d_bytes_per_step": total * 4, "d2h_bytes_per_step": total * 4,
-               "path": "pinned host -> HBM copy, PowerSGDReducer.reduce(), grad_out HBM -> pinned host"}
+               "path": "per step: pinned host -> HBM copy of all gradients, PowerSGDReducer.reduce(), grad_out HBM -> "
+                       "pinned host; copies of neighbouring steps overlap on the two copy engines"}
     if sampler:
         sampler.stop()
 
@@ -337,14 +377,12 @@ def run_b200(args):
     algo = {"pack": st["e_1"] * 8, "p_from_m": st["k1_bytes"], "orthogonalize": st["k2_bytes"],
             "q_from_mt": st["k3_bytes"], "q_reduce": 8 * st["e_q"], "finalize": st["k4_bytes"], "finish": st["e_1"] * 8}
     kernel_ms = 0.0
-    for name, (msum, cnt) in phases.items():
+    for name, (msum, cnt) in all_phases.items():
         if cnt:
             avg = msum / cnt
-            calls_per_step = cnt / K
-            kernel_ms += avg * calls_per_step
-            phase_report[name] = {"ms": round(avg, 5), "GBps": round(algo[name] / (avg * 1e-3) / 1e9, 1),
-                                  "calls_per_step": calls_per_step}
-    if "finalize" in phase_report:
+            kernel_ms += avg
+            phase_report[name] = {"ms": round(avg, 5), "GBps": round(algo[name] / (avg * 1e-3) / 1e9, 1)}
+    if phases.get("finalize", (0, 0))[1]:
         avg = phases["finalize"][0] / phases["finalize"][1]
         achieved = st["k4_bytes"] / (avg * 1e-3) / 1e9
         traffic = None
@@ -354,9 +392,10 @@ def run_b200(args):
         roofline = {"bound": "hbm", "kernel": "k_finalize (out = P Q^T, mem = M - out)", "achieved": achieved,
                     "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                     "algorithmic_bytes_per_launch": st["k4_bytes"], "ms_per_launch": avg, "peak_source": peak_src,
-                    "all_kernels": {"ms_per_step": kernel_ms,
-                                    "achieved": st["algo_bytes"] / (kernel_ms * 1e-3) / 1e9 if kernel_ms else None,
-                                    "frac": st["algo_bytes"] / (kernel_ms * 1e-3) / 1e9 / peak if kernel_ms else None}}
+                    "whole_step": {"ms_per_step": ms_per_step,
+                                   "achieved": st["algo_bytes"] / (ms_per_step * 1e-3) / 1e9,
+                                   "frac": st["algo_bytes"] / (ms_per_step * 1e-3) / 1e9 / peak,
+                                   "note": "all kernels + launch gaps of one reduce(), algorithmic bytes of SURVEY 8(d)"}}
 
     cpu = None
     if world == 1 and not args.skip_cpu_baseline:
@@ -372,6 +411,9 @@ def run_b200(args):
         "dtype": "f32", "data": "synthetic", "config": workload_config(args, st),
         "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
         "clocks": clocks, "phases": phase_report,
+        "phases_note": "per-phase event brackets measured in a separate pass (they add ~13 % to the step); "
+                       "only finalize is bracketed inside the timed region",
+        "host_issue_us_per_step": round(host_us, 1),
         "algorithmic_GBps": world * st["algo_bytes"] / (ms_per_step * 1e-3) / 1e9,
         "hbm_roofline_frac_whole_step": st["algo_bytes"] / (ms_per_step * 1e-3) / 1e9 / peak,
     }

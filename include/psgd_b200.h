@@ -103,8 +103,10 @@ int psgd_finalize(psgd_plan* plan, const float* p_mem, const float* q_mem, float
 int psgd_finish(psgd_plan* plan, const float* flat, float* q_mem, float n_workers,
                 psgd_stream stream);
 
-/* per-phase device timing with CUDA events on the launch stream (bench.py roofline) */
-int psgd_timing_enable(psgd_plan* plan, int on);
+/* per-phase device timing with CUDA events on the launch stream (bench.py roofline): `mask` bit k
+ * brackets phase k (PSGD_PHASE_*) with a pair of events, 0 switches timing off.  Each bracketed phase costs
+ * a few microseconds of stream time, so the benchmark brackets only the dominant kernel in its timed region. */
+int psgd_timing_enable(psgd_plan* plan, int mask);
 /* synchronises the recorded events; ms_sum/count have PSGD_N_PHASES entries; resets */
 int psgd_timing_read(psgd_plan* plan, double* ms_sum, int64_t* count);
 /* development aid: with PSGD_STREAM_DEBUG=1 in the environment at plan creation the streamed P = M Q

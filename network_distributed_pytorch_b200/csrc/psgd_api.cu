@@ -64,7 +64,9 @@ struct psgd_plan {
   std::vector<MatDesc> mats;
   std::vector<int4> tiles1, tiles4;
   std::vector<ColTile> tiles3;
-  std::vector<long long> q_pre, v_pre;
+  std::vector<long long> v_pre;
+  std::vector<VecTile> vtiles;
+  std::vector<QTile> qtiles;
   long long p_total = 0, q_total = 0, v_total = 0, ws_total = 0;
   int wc_cap = 0;
   int n_max = 0;
@@ -85,13 +87,14 @@ struct psgd_plan {
   int4* d_tiles4_fb = nullptr;
   int stream_grid = 148, ring_slot_bytes = 0, ring_slots = 0, q_bytes = 0;
   size_t stream_smem = 0;
+  bool attr1_set = false, attr4_set = false;  // opt-in shared memory size set on the streamed kernels
   // device tables
   MatDesc* d_mats = nullptr;
   int4* d_tiles1 = nullptr;
   int4* d_tiles4 = nullptr;
   ColTile* d_tiles3 = nullptr;
-  long long* d_q_pre = nullptr;
-  long long* d_v_pre = nullptr;
+  VecTile* d_vtiles = nullptr;
+  QTile* d_qtiles = nullptr;
   // pointer ring
   size_t slot_bytes = 0;
   char* h_ring = nullptr;
@@ -102,7 +105,7 @@ struct psgd_plan {
   PtrSlot slot{};
   bool have_ge = false;
   // timing
-  bool timing = false;
+  unsigned timing = 0;  // bit k set: phase k is bracketed by events
   std::vector<Timer> timers;
   std::vector<Timer> free_timers;
   double ms_sum[PSGD_N_PHASES] = {};
@@ -114,7 +117,8 @@ struct psgd_tb {
   int n = 0, elem_size = 4;
   long long total = 0;
   std::vector<long long> pre;
-  long long* d_pre = nullptr;
+  std::vector<VecTile> tiles;
+  VecTile* d_tiles = nullptr;
   size_t slot_bytes = 0;
   char* h_ring = nullptr;
   char* d_ring = nullptr;
@@ -131,8 +135,8 @@ DevPlan dev_plan(const psgd_plan* p) {
   d.tiles1 = p->d_tiles1;
   d.tiles4 = p->d_tiles4;
   d.tiles3 = p->d_tiles3;
-  d.q_pre = p->d_q_pre;
-  d.v_pre = p->d_v_pre;
+  d.vtiles = p->d_vtiles;
+  d.qtiles = p->d_qtiles;
   d.n_mat = p->n_mat;
   d.n_vec = p->n_vec;
   d.wc_cap = p->wc_cap;
@@ -220,7 +224,7 @@ struct PhaseScope {
   Timer t{};
   bool on = false;
   PhaseScope(psgd_plan* plan, int phase, cudaStream_t st) : p(plan), s(st) {
-    if (!p->timing) return;
+    if (!((p->timing >> phase) & 1u)) return;
     if (!p->free_timers.empty()) {
       t = p->free_timers.back();
       p->free_timers.pop_back();
@@ -308,7 +312,6 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
   const int cgw_cap = (int)env_ll("PSGD_T3_CGW", 128);
 
   p->mats.resize(n_mat);
-  p->q_pre.assign(n_mat + 1, 0);
   long long po = 0, qo = 0, wo = 0;
   int mmax = 0;
   size_t smem3 = 0;
@@ -323,7 +326,14 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
     md.pad_ = 0;
     po += (long long)md.n * md.r;  // reducer.py:97
     qo += (long long)md.m * md.r;  // reducer.py:98
-    p->q_pre[i + 1] = qo;
+    for (long long e0 = 0; e0 < (long long)md.m * md.r; e0 += kQTileElems) {
+      QTile qt;
+      qt.mat = i;
+      qt.e0 = (int)e0;
+      qt.count = (int)std::min<long long>(kQTileElems, (long long)md.m * md.r - e0);
+      qt.pad_ = 0;
+      if (md.n > 0) p->qtiles.push_back(qt);
+    }
     mmax = std::max(mmax, md.m);
     p->n_max = std::max(p->n_max, md.n);
 
@@ -430,6 +440,15 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
       return fail("vector %d has negative length", j);
     }
     p->v_pre[j + 1] = p->v_pre[j] + vec_len[j];  // tensor_buffer.py:11-13
+    for (long long st = 0; st < vec_len[j]; st += kVecTileElems) {
+      VecTile vt;
+      vt.flat_off = p->v_pre[j] + st;
+      vt.tensor = j;
+      vt.start = (int)st;
+      vt.count = (int)std::min<long long>(kVecTileElems, vec_len[j] - st);
+      vt.pad_ = 0;
+      p->vtiles.push_back(vt);
+    }
   }
   p->v_total = p->v_pre[n_vec];
 
@@ -444,8 +463,8 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
     rc |= upload(&p->d_tiles1, p->tiles1);
     rc |= upload(&p->d_tiles4, p->tiles4);
     rc |= upload(&p->d_tiles3, p->tiles3);
-    rc |= upload(&p->d_q_pre, p->q_pre);
-    rc |= upload(&p->d_v_pre, p->v_pre);
+    rc |= upload(&p->d_vtiles, p->vtiles);
+    rc |= upload(&p->d_qtiles, p->qtiles);
     rc |= upload(&p->d_tasks1, p->tasks1);
     rc |= upload(&p->d_tasks4, p->tasks4);
     if (!rc && cudaMalloc((void**)&p->d_counters, 4 * sizeof(int)) != cudaSuccess) rc = fail("cudaMalloc(counters) failed");
@@ -487,8 +506,8 @@ int psgd_plan_destroy(psgd_plan* p) {
     cudaFree(p->d_tiles1);
     cudaFree(p->d_tiles4);
     cudaFree(p->d_tiles3);
-    cudaFree(p->d_q_pre);
-    cudaFree(p->d_v_pre);
+    cudaFree(p->d_vtiles);
+    cudaFree(p->d_qtiles);
     cudaFree(p->d_tasks1);
     cudaFree(p->d_tasks4);
     cudaFree(p->d_counters);
@@ -628,9 +647,8 @@ int psgd_pack_vec(psgd_plan* p, float* flat, psgd_stream stream) {
   CU(cudaSetDevice(p->device));
   cudaStream_t s = (cudaStream_t)stream;
   PhaseScope ts(p, PSGD_PHASE_PACK, s);
-  const unsigned grid = (unsigned)((p->v_total + kThreads - 1) / kThreads);
-  k_gather<uint32_t><<<grid, kThreads, 0, s>>>(p->d_v_pre, p->n_vec, (const void* const*)p->slot.vin,
-                                                (uint32_t*)flat, p->v_total);
+  k_gather<uint32_t><<<(unsigned)p->vtiles.size(), kThreads, 0, s>>>(p->d_vtiles, (const void* const*)p->slot.vin,
+                                                                      (uint32_t*)flat);
   return check_launch("k_gather");
 }
 
@@ -677,7 +695,8 @@ int psgd_p_from_m(psgd_plan* p, float* p_mem, const float* q_mem, int fuse_add, 
   if (!fuse_add && p->stream1_now) {
     StreamPlan sp{p->d_tasks1, p->d_counters, (int)p->tasks1.size(), p->ring_slot_bytes, p->ring_slots, p->q_bytes, p->d_dbg};
     DISPATCH_R(p->R, {
-      CU(cudaFuncSetAttribute((const void*)k_p_from_m_stream<RR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->stream_smem));
+      if (!p->attr1_set) CU(cudaFuncSetAttribute((const void*)k_p_from_m_stream<RR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->stream_smem));
+      p->attr1_set = true;
       k_p_from_m_stream<RR><<<p->stream_grid, kStreamThreads, p->stream_smem, s>>>(dp, p->slot, sp, q_mem, p_mem, q_div);
     });
     if (check_launch("k_p_from_m_stream")) return 1;
@@ -774,8 +793,7 @@ int psgd_q_from_mt(psgd_plan* p, const float* p_mem, float* q_mem, void* workspa
   }
   {
     PhaseScope ts(p, PSGD_PHASE_Q_REDUCE, s);
-    const unsigned grid = (unsigned)((p->q_total + kThreads - 1) / kThreads);
-    k_q_reduce<<<grid, kThreads, 0, s>>>(dp, ws, q_mem, p->q_total);
+    k_q_reduce<<<(unsigned)p->qtiles.size(), kThreads, 0, s>>>(dp, ws, q_mem);
     if (check_launch("k_q_reduce")) return 1;
   }
   return 0;
@@ -794,7 +812,8 @@ int psgd_finalize(psgd_plan* p, const float* p_mem, const float* q_mem, float n_
   if (p->stream4_now) {
     StreamPlan sp{p->d_tasks4, p->d_counters + 2, (int)p->tasks4.size(), p->ring_slot_bytes, p->ring_slots, p->q_bytes, nullptr};
     DISPATCH_R(p->R, {
-      CU(cudaFuncSetAttribute((const void*)k_finalize_stream<RR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->stream_smem));
+      if (!p->attr4_set) CU(cudaFuncSetAttribute((const void*)k_finalize_stream<RR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->stream_smem));
+      p->attr4_set = true;
       k_finalize_stream<RR><<<p->stream_grid, kStreamThreads, p->stream_smem, s>>>(dp, p->slot, sp, p_mem, q_mem, n_workers);
     });
     if (check_launch("k_finalize_stream")) return 1;
@@ -826,14 +845,14 @@ int psgd_finish(psgd_plan* p, const float* flat, float* q_mem, float n_workers, 
   CU(cudaSetDevice(p->device));
   cudaStream_t s = (cudaStream_t)stream;
   PhaseScope ts(p, PSGD_PHASE_FINISH, s);
-  const unsigned grid = (unsigned)((total + kThreads - 1) / kThreads);
-  k_finish<<<grid, kThreads, 0, s>>>(dev_plan(p), p->slot, flat, p->v_total, q_mem, qn, n_workers);
+  const unsigned grid = (unsigned)(p->vtiles.size() + (size_t)((qn + kVecTileElems - 1) / kVecTileElems));
+  k_finish<<<grid, kThreads, 0, s>>>(dev_plan(p), p->slot, flat, (int)p->vtiles.size(), q_mem, qn, n_workers);
   return check_launch("k_finish");
 }
 
 int psgd_timing_enable(psgd_plan* p, int on) {
   if (need_device(p)) return 1;
-  p->timing = on != 0;
+  p->timing = on < 0 ? 0u : (unsigned)on;
   return 0;
 }
 
@@ -883,12 +902,21 @@ int psgd_tb_create(int n, const int64_t* nelem, int elem_size, int device, psgd_
   for (int i = 0; i < n; ++i) {
     if (nelem[i] < 0) { delete tb; return fail("psgd_tb_create: negative length"); }
     tb->pre[i + 1] = tb->pre[i] + nelem[i];
+    for (long long st = 0; st < nelem[i]; st += kVecTileElems) {
+      VecTile vt;
+      vt.flat_off = tb->pre[i] + st;
+      vt.tensor = i;
+      vt.start = (int)st;
+      vt.count = (int)std::min<long long>(kVecTileElems, nelem[i] - st);
+      vt.pad_ = 0;
+      tb->tiles.push_back(vt);
+    }
   }
   tb->total = tb->pre[n];
   tb->slot_bytes = std::max<size_t>(256, ((size_t)n * 8 + 255) & ~(size_t)255);
   int rc = 0;
   if (cudaSetDevice(device) != cudaSuccess) rc = fail("cudaSetDevice(%d) failed", device);
-  if (!rc) rc = upload(&tb->d_pre, tb->pre);
+  if (!rc) rc = upload(&tb->d_tiles, tb->tiles);
   if (!rc && cudaMallocHost((void**)&tb->h_ring, tb->slot_bytes * kSlots) != cudaSuccess) rc = fail("cudaMallocHost failed");
   if (!rc && cudaMalloc((void**)&tb->d_ring, tb->slot_bytes * kSlots) != cudaSuccess) rc = fail("cudaMalloc failed");
   for (int s = 0; s < kSlots && !rc; ++s)
@@ -906,7 +934,7 @@ int psgd_tb_create(int n, const int64_t* nelem, int elem_size, int device, psgd_
 int psgd_tb_destroy(psgd_tb* tb) {
   if (!tb) return 0;
   cudaSetDevice(tb->device);
-  cudaFree(tb->d_pre);
+  cudaFree(tb->d_tiles);
   cudaFree(tb->d_ring);
   if (tb->h_ring) cudaFreeHost(tb->h_ring);
   for (int s = 0; s < kSlots; ++s)
@@ -941,12 +969,12 @@ int psgd_tb_pack(psgd_tb* tb, const void* const* src, void* flat, psgd_stream st
   cudaStream_t s = (cudaStream_t)stream;
   void** d = nullptr;
   if (tb_upload(tb, src, s, &d)) return 1;
-  const unsigned grid = (unsigned)((tb->total + kThreads - 1) / kThreads);
+  const unsigned grid = (unsigned)tb->tiles.size();
   switch (tb->elem_size) {
-    case 1: k_gather<uint8_t><<<grid, kThreads, 0, s>>>(tb->d_pre, tb->n, (const void* const*)d, (uint8_t*)flat, tb->total); break;
-    case 2: k_gather<uint16_t><<<grid, kThreads, 0, s>>>(tb->d_pre, tb->n, (const void* const*)d, (uint16_t*)flat, tb->total); break;
-    case 4: k_gather<uint32_t><<<grid, kThreads, 0, s>>>(tb->d_pre, tb->n, (const void* const*)d, (uint32_t*)flat, tb->total); break;
-    default: k_gather<uint64_t><<<grid, kThreads, 0, s>>>(tb->d_pre, tb->n, (const void* const*)d, (uint64_t*)flat, tb->total); break;
+    case 1: k_gather<uint8_t><<<grid, kThreads, 0, s>>>(tb->d_tiles, (const void* const*)d, (uint8_t*)flat); break;
+    case 2: k_gather<uint16_t><<<grid, kThreads, 0, s>>>(tb->d_tiles, (const void* const*)d, (uint16_t*)flat); break;
+    case 4: k_gather<uint32_t><<<grid, kThreads, 0, s>>>(tb->d_tiles, (const void* const*)d, (uint32_t*)flat); break;
+    default: k_gather<uint64_t><<<grid, kThreads, 0, s>>>(tb->d_tiles, (const void* const*)d, (uint64_t*)flat); break;
   }
   return check_launch("k_gather");
 }
@@ -959,12 +987,12 @@ int psgd_tb_unpack(psgd_tb* tb, const void* flat, void* const* dst, psgd_stream 
   cudaStream_t s = (cudaStream_t)stream;
   void** d = nullptr;
   if (tb_upload(tb, (const void* const*)dst, s, &d)) return 1;
-  const unsigned grid = (unsigned)((tb->total + kThreads - 1) / kThreads);
+  const unsigned grid = (unsigned)tb->tiles.size();
   switch (tb->elem_size) {
-    case 1: k_scatter<uint8_t><<<grid, kThreads, 0, s>>>(tb->d_pre, tb->n, (const uint8_t*)flat, (void* const*)d, tb->total); break;
-    case 2: k_scatter<uint16_t><<<grid, kThreads, 0, s>>>(tb->d_pre, tb->n, (const uint16_t*)flat, (void* const*)d, tb->total); break;
-    case 4: k_scatter<uint32_t><<<grid, kThreads, 0, s>>>(tb->d_pre, tb->n, (const uint32_t*)flat, (void* const*)d, tb->total); break;
-    default: k_scatter<uint64_t><<<grid, kThreads, 0, s>>>(tb->d_pre, tb->n, (const uint64_t*)flat, (void* const*)d, tb->total); break;
+    case 1: k_scatter<uint8_t><<<grid, kThreads, 0, s>>>(tb->d_tiles, (const uint8_t*)flat, (void* const*)d); break;
+    case 2: k_scatter<uint16_t><<<grid, kThreads, 0, s>>>(tb->d_tiles, (const uint16_t*)flat, (void* const*)d); break;
+    case 4: k_scatter<uint32_t><<<grid, kThreads, 0, s>>>(tb->d_tiles, (const uint32_t*)flat, (void* const*)d); break;
+    default: k_scatter<uint64_t><<<grid, kThreads, 0, s>>>(tb->d_tiles, (const uint64_t*)flat, (void* const*)d); break;
   }
   return check_launch("k_scatter");
 }

@@ -31,6 +31,19 @@ struct ColTile {
   int blk, pad0, pad1, pad2;
 };
 
+// flat-buffer tile: `count` elements of tensor `tensor` starting at `start`, living at `flat_off`
+struct VecTile {
+  long long flat_off;
+  int tensor, start, count, pad_;
+};
+constexpr int kVecTileElems = 2048;
+
+// K3 stage-2 tile: `count` consecutive Q elements of matrix `mat` starting at local element `e0`
+struct QTile {
+  int mat, e0, count, pad_;
+};
+constexpr int kQTileElems = 1024;
+
 // device views of the per-step pointer arrays (one ring slot)
 struct PtrSlot {
   const float* const* in;   // M_i   (grad_in,  reducer.py:43)
@@ -54,8 +67,8 @@ struct DevPlan {
   const int4* tiles1;      // K1 row tiles {mat, row0, nrows, -}
   const int4* tiles4;      // K4 row tiles
   const ColTile* tiles3;   // K3 tiles
-  const long long* q_pre;  // n_mat + 1 prefix of q offsets
-  const long long* v_pre;  // n_vec + 1 prefix of vector offsets
+  const VecTile* vtiles;   // tiles of the flat <=1-D buffer
+  const QTile* qtiles;     // tiles of q_mem for the K3 second stage
   int n_mat, n_vec;
   int wc_cap;              // max columns of Q staged in shared memory at once
   int pad_;

@@ -538,27 +538,44 @@ k_q_from_mt(DevPlan pl, PtrSlot ps, const float* __restrict__ p_mem, float* __re
   }
 }
 
-// stage 2: q_mem[e] = sum over row blocks, in block order
+// stage 2: q_mem[e] = sum over row blocks, in block order.  One tile = kQTileElems consecutive elements
+// of one matrix; a thread owns 4 of them and keeps 4 row blocks in flight.
 __global__ void __launch_bounds__(kThreads)
-k_q_reduce(DevPlan pl, const float* __restrict__ ws, float* __restrict__ q_mem, long long q_total) {
-  const long long e = (long long)blockIdx.x * kThreads + threadIdx.x;
-  if (e >= q_total) return;
-  const int mat = find_segment(pl.q_pre, pl.n_mat, e);
-  const MatDesc md = pl.mats[mat];
-  const long long local = e - md.q_off;
+k_q_reduce(DevPlan pl, const float* __restrict__ ws, float* __restrict__ q_mem) {
+  const QTile t = pl.qtiles[blockIdx.x];
+  const MatDesc md = pl.mats[t.mat];
   const size_t stride = (size_t)md.m * md.r;
-  const float* src = ws + md.ws_off + local;
-  float s = 0.f;
-  int b = 0;
-  for (; b + 4 <= md.nblk3; b += 4) {
-    const float v0 = src[(size_t)b * stride];
-    const float v1 = src[(size_t)(b + 1) * stride];
-    const float v2 = src[(size_t)(b + 2) * stride];
-    const float v3 = src[(size_t)(b + 3) * stride];
-    s = ((s + v0) + v1) + v2 + v3;
+  const int e = t.e0 + threadIdx.x * 4;
+  if (e >= t.e0 + t.count) return;
+  const float* src = ws + md.ws_off + e;
+  float* dst = q_mem + md.q_off + e;
+  const int nb = md.nblk3;
+  if ((stride & 3) == 0 && e + 4 <= t.e0 + t.count) {
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    int b = 0;
+    for (; b + 4 <= nb; b += 4) {
+      const float4 v0 = *reinterpret_cast<const float4*>(src + (size_t)b * stride);
+      const float4 v1 = *reinterpret_cast<const float4*>(src + (size_t)(b + 1) * stride);
+      const float4 v2 = *reinterpret_cast<const float4*>(src + (size_t)(b + 2) * stride);
+      const float4 v3 = *reinterpret_cast<const float4*>(src + (size_t)(b + 3) * stride);
+      s.x = (((s.x + v0.x) + v1.x) + v2.x) + v3.x;
+      s.y = (((s.y + v0.y) + v1.y) + v2.y) + v3.y;
+      s.z = (((s.z + v0.z) + v1.z) + v2.z) + v3.z;
+      s.w = (((s.w + v0.w) + v1.w) + v2.w) + v3.w;
+    }
+    for (; b < nb; ++b) {
+      const float4 v = *reinterpret_cast<const float4*>(src + (size_t)b * stride);
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    dst[0] = s.x; dst[1] = s.y; dst[2] = s.z; dst[3] = s.w;
+  } else {
+    const int lim = min(4, t.e0 + t.count - e);
+    for (int x = 0; x < lim; ++x) {
+      float s = 0.f;
+      for (int b = 0; b < nb; ++b) s += src[(size_t)b * stride + x];
+      dst[x] = s;
+    }
   }
-  for (; b < md.nblk3; ++b) s += src[(size_t)b * stride];
-  q_mem[e] = s;
 }
 
 // =======================================================================================
@@ -656,42 +673,49 @@ k_finalize(DevPlan pl, PtrSlot ps, const float* __restrict__ p_mem, const float*
 }
 
 // =======================================================================================
-// K6: flat-buffer gather / scatter of the <=1-D tensors (tensor_buffer.py:19,34-36) as one
-// kernel over a pointer table; T is the element word (1/2/4/8 bytes) so TensorBuffer keeps
-// the upstream "dtype follows the inputs" behaviour bit-exactly.
+// K6: flat-buffer gather / scatter of the <=1-D tensors (tensor_buffer.py:19,34-36) as one kernel over
+// a pointer table and a tile table (one CTA = up to kVecTileElems elements of one tensor, no search);
+// T is the element word (1/2/4/8 bytes) so TensorBuffer keeps the upstream "dtype follows the inputs"
+// behaviour bit-exactly.
 // =======================================================================================
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
-k_gather(const long long* __restrict__ pre, int n, const void* const* __restrict__ src, T* __restrict__ flat,
-         long long total) {
-  const long long e = (long long)blockIdx.x * kThreads + threadIdx.x;
-  if (e >= total) return;
-  const int t = find_segment(pre, n, e);
-  flat[e] = static_cast<const T*>(src[t])[e - __ldg(pre + t)];
+k_gather(const VecTile* __restrict__ tiles, const void* const* __restrict__ src, T* __restrict__ flat) {
+  const VecTile t = tiles[blockIdx.x];
+  const T* s = static_cast<const T*>(src[t.tensor]) + t.start;
+  T* d = flat + t.flat_off;
+  for (int i = threadIdx.x; i < t.count; i += kThreads) d[i] = s[i];
 }
 
 template <typename T>
 __global__ void __launch_bounds__(kThreads)
-k_scatter(const long long* __restrict__ pre, int n, const T* __restrict__ flat, void* const* __restrict__ dst,
-          long long total) {
-  const long long e = (long long)blockIdx.x * kThreads + threadIdx.x;
-  if (e >= total) return;
-  const int t = find_segment(pre, n, e);
-  static_cast<T*>(dst[t])[e - __ldg(pre + t)] = flat[e];
+k_scatter(const VecTile* __restrict__ tiles, const T* __restrict__ flat, void* const* __restrict__ dst) {
+  const VecTile t = tiles[blockIdx.x];
+  T* d = static_cast<T*>(dst[t.tensor]) + t.start;
+  const T* s = flat + t.flat_off;
+  for (int i = threadIdx.x; i < t.count; i += kThreads) d[i] = s[i];
 }
 
-// K6b: vec_out = flat / n_workers (reducer.py:167-168) and q_mem /= n_workers (reducer.py:147)
+// K6b: vec_out = flat / n_workers (reducer.py:167-168); blocks past the vector tiles scale q_mem in place
+// (q_mem /= n_workers, reducer.py:147)
 __global__ void __launch_bounds__(kThreads)
-k_finish(DevPlan pl, PtrSlot ps, const float* __restrict__ flat, long long v_total, float* __restrict__ q_mem,
+k_finish(DevPlan pl, PtrSlot ps, const float* __restrict__ flat, int n_vtiles, float* __restrict__ q_mem,
          long long q_total, float world) {
-  const long long e = (long long)blockIdx.x * kThreads + threadIdx.x;
-  if (e < v_total) {
-    const int t = find_segment(pl.v_pre, pl.n_vec, e);
-    float v = flat[e];
-    if (world != 1.0f) v = v / world;
-    ps.vout[t][e - __ldg(pl.v_pre + t)] = v;
-  } else if (e - v_total < q_total) {
-    q_mem[e - v_total] = q_mem[e - v_total] / world;
+  if ((int)blockIdx.x < n_vtiles) {
+    const VecTile t = pl.vtiles[blockIdx.x];
+    float* d = ps.vout[t.tensor] + t.start;
+    const float* s = flat + t.flat_off;
+    if (world != 1.0f) {
+      for (int i = threadIdx.x; i < t.count; i += kThreads) d[i] = s[i] / world;
+    } else {
+      for (int i = threadIdx.x; i < t.count; i += kThreads) d[i] = s[i];
+    }
+  } else {
+    const long long base = (long long)(blockIdx.x - n_vtiles) * kVecTileElems;
+    for (int i = threadIdx.x; i < kVecTileElems; i += kThreads) {
+      const long long e = base + i;
+      if (e < q_total) q_mem[e] = q_mem[e] / world;
+    }
   }
 }
 

@@ -280,7 +280,7 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
   int cur_mat = -1, m = 0, r = 0, pitch = 0;
   float* P = nullptr;
   const bool dbg = sp.dbg != nullptr && threadIdx.x == 0;
-  unsigned long long d_t0 = 0, d_desc = 0, d_data = 0, d_q = 0, d_units = 0, d_sw = 0;
+  unsigned long long d_t0 = 0, d_desc = 0, d_data = 0, d_q = 0, d_units = 0, d_sw = 0, d_work = 0;
   long long c0 = 0, c_begin = 0;
   if (dbg) { d_t0 = gtime_ns(); c_begin = clock64(); }
   for (int it = 0;; ++it) {
@@ -310,14 +310,17 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
       continue;
     }
     const int nsub = (u_n + ROWS - 1) / ROWS;
-    // sub-span j of this unit belongs to warp (rot + j) % kConsumerWarps; a warp without a sub-span skips
-    // the unit altogether (its share of the slot's release count is handed in by the j == 0 warp), so the
-    // release of a slot depends only on the warps that actually read it
+    // sub-span j of this unit belongs to warp (rot + j) % kConsumerWarps.  Every warp arrives on every
+    // unit, with or without a sub-span: that keeps any slot's barriers within one lap of every warp (a
+    // warp that skipped arrivals could find a slot two laps ahead and mis-read the parity).
     const int j0 = (warp - u_w % kConsumerWarps + kConsumerWarps) % kConsumerWarps;
-    if (j0 >= nsub) continue;
+    if (j0 >= nsub) {
+      if (lane == 0) mbar_arrive(&sm.empty[slot]);
+      continue;
+    }
     if (dbg) c0 = clock64();
     mbar_wait(&sm.full[slot], phase);
-    if (dbg) { d_data += clock64() - c0; ++d_units; }
+    if (dbg) { d_data += clock64() - c0; ++d_units; c0 = clock64(); }
     const int kmax = m >> 2;
     for (int j = j0; j < nsub; j += kConsumerWarps) {
       const int rbase = j * ROWS;
@@ -361,12 +364,13 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
       }
     }
     __syncwarp();
-    if (lane == 0) mbar_arrive_n(&sm.empty[slot], (j0 == 0 && nsub < kConsumerWarps) ? 1 + kConsumerWarps - nsub : 1);
+    if (lane == 0) mbar_arrive(&sm.empty[slot]);
+    if (dbg) d_work += clock64() - c0;
   }
   if (dbg) {
     unsigned long long* o = sp.dbg + (size_t)blockIdx.x * kDbgWords;
     o[0] = d_t0; o[1] = gtime_ns(); o[2] = d_desc; o[3] = d_data; o[4] = d_q;
-    o[5] = (unsigned long long)(clock64() - c_begin); o[6] = d_units; o[7] = d_sw;
+    o[5] = (unsigned long long)(clock64() - c_begin); o[6] = d_units; o[7] = d_work;
   }
 }
 
@@ -418,7 +422,10 @@ k_finalize_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
     }
     const int nsub = (u_n + ROWS - 1) / ROWS;
     const int j0 = (warp - u_w % kConsumerWarps + kConsumerWarps) % kConsumerWarps;
-    if (j0 >= nsub) continue;  // see k_p_from_m_stream
+    if (j0 >= nsub) {  // see k_p_from_m_stream
+      if (lane == 0) mbar_arrive(&sm.empty[slot]);
+      continue;
+    }
     const int kmax = m >> 2;
     bool landed = false;
     for (int j = j0; j < nsub; j += kConsumerWarps) {
@@ -460,7 +467,7 @@ k_finalize_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
       }
     }
     __syncwarp();
-    if (lane == 0) mbar_arrive_n(&sm.empty[slot], (j0 == 0 && nsub < kConsumerWarps) ? 1 + kConsumerWarps - nsub : 1);
+    if (lane == 0) mbar_arrive(&sm.empty[slot]);
   }
 }
 

@@ -100,8 +100,15 @@ class CudaPlan:
                                          _stream(self.device)), self._lib)
 
     # -- timing -----------------------------------------------------------------------------
-    def timing_enable(self, on=True):
-        _lib.check(self._lib.psgd_timing_enable(self._h, int(on)), self._lib)
+    def timing_enable(self, phases=True):
+        """phases: True = all, False = off, or an iterable of phase names (see _lib.PHASE_NAMES)."""
+        if phases is True:
+            mask = (1 << _lib.N_PHASES) - 1
+        elif not phases:
+            mask = 0
+        else:
+            mask = sum(1 << _lib.PHASE_NAMES.index(p) for p in phases)
+        _lib.check(self._lib.psgd_timing_enable(self._h, mask), self._lib)
 
     def timing_read(self):
         ms = (ctypes.c_double * _lib.N_PHASES)()

@@ -30,5 +30,5 @@ t0 = a[:, 0].min()
 print("CTAs", len(a))
 print("start spread ns: max-min", a[:, 0].max() - t0)
 print("end   ns rel: min %.0f mean %.0f max %.0f" % ((a[:, 1] - t0).min(), (a[:, 1] - t0).mean(), (a[:, 1] - t0).max()))
-for k, name in ((5, "total cycles"), (2, "desc wait"), (3, "data wait"), (4, "Q stage"), (6, "units"), (7, "switches")):
+for k, name in ((5, "total cycles"), (2, "desc wait"), (3, "data wait"), (4, "Q stage"), (6, "units"), (7, "work cycles")):
     print("%-12s min %9.0f mean %9.0f max %9.0f" % (name, a[:, k].min(), a[:, k].mean(), a[:, k].max()))
