@@ -126,6 +126,21 @@ int psgd_tb_unpack(psgd_tb* tb, const void* flat, void* const* dst, psgd_stream 
  * orthogonalize(matrix) of reducer.py:180-191. */
 int psgd_orthogonalize_one(float* mat, int64_t n, int r, int device, psgd_stream stream);
 
+/* No counterpart in the reference (which allocates freely through PyTorch).  Q = M^T P for ONE n x m
+ * row-major fp32 matrix (p_hat: n x r, q_out: m x r, both row-major) without a plan and without any
+ * allocation, for callers that cannot obtain device memory at this point: a process whose framework
+ * allocator already owns the GPU, a hot loop that must not take the device-wide synchronisation of
+ * cudaMalloc / cudaFree, a host that forbids driver allocations after start-up.  The split-n partial sums
+ * live in an array built into the library (PSGD_NOALLOC_SCRATCH_BYTES per GPU, held until exit).
+ * Limit: ceil(n / T) * m * r * 4 bytes must fit that array, T = clamp(ceil(n / 32), 128, 512); larger
+ * requests fail with a message naming both numbers.  The first call on a device looks the array's address
+ * up and should be made before any stream capture starts.  All calls share the array: nothing in it needs
+ * clearing between calls (every partial that is read is overwritten first), but calls that overlap on the
+ * GPU race -- keep them on one stream or order them. */
+#define PSGD_NOALLOC_SCRATCH_BYTES (4 * 1024 * 1024)
+int psgd_q_from_mt_noalloc(const float* mat, const float* p_hat, float* q_out, int64_t n, int64_t m,
+                           int r, int device, psgd_stream stream);
+
 #ifdef __cplusplus
 }
 #endif

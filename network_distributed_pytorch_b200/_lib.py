@@ -45,6 +45,7 @@ SIGNATURES = {
     "psgd_tb_pack": (ctypes.c_int, [vp, vp, vp, vp]),
     "psgd_tb_unpack": (ctypes.c_int, [vp, vp, vp, vp]),
     "psgd_orthogonalize_one": (ctypes.c_int, [vp, ctypes.c_int64, ctypes.c_int, ctypes.c_int, vp]),
+    "psgd_q_from_mt_noalloc": (ctypes.c_int, [vp, vp, vp, ctypes.c_int64, ctypes.c_int64, ctypes.c_int, ctypes.c_int, vp]),
 }
 
 _lib = None

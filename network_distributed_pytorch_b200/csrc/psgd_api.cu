@@ -1011,3 +1011,131 @@ int psgd_orthogonalize_one(float* mat, int64_t n, int r, int device, psgd_stream
 }
 
 }  // extern "C"
+
+// =======================================================================================================
+// psgd_q_from_mt_noalloc: Q = M^T P for one matrix without a plan and without a single allocation.
+//
+// Who needs this: code that runs where device memory can no longer be requested.  Typical cases are a
+// process whose framework allocator has already claimed the GPU (a raw cudaMalloc from a plug-in then fails
+// or eats into a budget somebody else manages), a latency-critical inner loop that cannot afford the
+// device-wide synchronisation cudaMalloc / cudaFree imply, and hosts that forbid driver allocations after
+// start-up.  Such a caller still owns its inputs and its output; what it cannot supply is the scratch space
+// the split-n reduction needs for its per-row-block partial sums.  Here that scratch is a fixed array inside
+// the library's device image: PSGD_NOALLOC_SCRATCH_BYTES on every GPU that loads the library, held until
+// the process exits.
+//
+// Rules that follow from sharing one array:
+//   * the first call on a device looks the array's device address up (cudaGetSymbolAddress, with that
+//     device current) and keeps it; make that first call before any stream capture begins;
+//   * requests whose partials do not fit are refused (the message states the bytes needed and the limit);
+//   * the array keeps whatever the previous call left in it.  Nothing has to start at zero: the first kernel
+//     overwrites every partial the second kernel reads, so stale contents are never observed;
+//   * two calls that overlap on the GPU (different streams, or different host threads on one device) would
+//     write the same partials: run them back to back on one stream, or order them yourself.
+// =======================================================================================================
+namespace {
+
+static __device__ __align__(256) float g_noalloc_scratch[PSGD_NOALLOC_SCRATCH_BYTES / sizeof(float)];
+
+constexpr int kNoAllocMaxDevices = 64;
+float* g_noalloc_ptr[kNoAllocMaxDevices] = {};  // device address of g_noalloc_scratch, per device
+std::atomic<bool> g_noalloc_ready[kNoAllocMaxDevices];
+
+// stage 1 for a single matrix: the tile geometry is derived from blockIdx instead of plan tables
+template <int R>
+__global__ void __launch_bounds__(kThreads, (R <= 8) ? 2 : 1)
+k_q_from_mt_single(const float* __restrict__ M, const float* __restrict__ P, float* __restrict__ scratch, int n, int m,
+                   int r, int cgw, int cpt, int t_rows, int ncol, int vec_ok) {
+  extern __shared__ __align__(16) float smem[];
+  MatDesc md;
+  md.p_off = 0; md.q_off = 0; md.ws_off = 0;
+  md.n = n; md.m = m; md.r = r;
+  md.cgw = cgw; md.cpt = cpt; md.t3_rows = t_rows;
+  md.nblk3 = (n + t_rows - 1) / t_rows;
+  md.pad_ = 0;
+  ColTile t;
+  t.mat = 0;
+  t.blk = (int)(blockIdx.x / ncol);
+  t.row0 = t.blk * t_rows;
+  t.nrows = min(t_rows, n - t.row0);
+  t.col0 = (int)(blockIdx.x % ncol) * cgw * cpt;
+  t.pad0 = t.pad1 = t.pad2 = 0;
+  if (cpt == 4) {
+    if (vec_ok) q_tile<R, 4, true>(md, t, M, P, scratch, smem);
+    else q_tile<R, 4, false>(md, t, M, P, scratch, smem);
+  } else {
+    q_tile<R, 1, false>(md, t, M, P, scratch, smem);
+  }
+}
+
+// stage 2 for a single matrix: Q[e] = sum of the row-block partials, in block order
+__global__ void __launch_bounds__(kThreads)
+k_q_reduce_single(const float* __restrict__ scratch, float* __restrict__ Q, long long mr, int nblk) {
+  const long long e = (long long)blockIdx.x * kThreads + threadIdx.x;
+  if (e >= mr) return;
+  float s = 0.f;
+  for (int b = 0; b < nblk; ++b) s += scratch[(size_t)b * mr + e];
+  Q[e] = s;
+}
+
+}  // namespace
+
+extern "C" int psgd_q_from_mt_noalloc(const float* mat, const float* p_hat, float* q_out, int64_t n, int64_t m, int r,
+                                      int device, psgd_stream stream) {
+  if (n < 0 || m < 0 || r < 0) return fail("psgd_q_from_mt_noalloc: negative shape");
+  if (n > 0x7fffffffLL || m > 0x7fffffffLL) return fail("psgd_q_from_mt_noalloc: shape out of range");
+  if (r > PSGD_MAX_RANK) return fail("psgd_q_from_mt_noalloc: r = %d exceeds PSGD_MAX_RANK = %d", r, PSGD_MAX_RANK);
+  if (r > n || r > m) return fail("psgd_q_from_mt_noalloc: r = %d exceeds min(n, m)", r);
+  if (device < 0 || device >= kNoAllocMaxDevices) return fail("psgd_q_from_mt_noalloc: device %d out of range", device);
+  if (m == 0 || r == 0) return 0;
+  if (!q_out || (n > 0 && (!mat || !p_hat))) return fail("psgd_q_from_mt_noalloc: null pointer");
+  if (((uintptr_t)mat | (uintptr_t)p_hat | (uintptr_t)q_out) & 3) return fail("psgd_q_from_mt_noalloc: pointers must be 4-byte aligned");
+
+  // row blocks of 128..512 rows; every block leaves one m x r partial in the scratch array
+  const int t_rows = (int)std::min<int64_t>(512, std::max<int64_t>(128, (n + 31) / 32));
+  const int nblk = n ? (int)((n + t_rows - 1) / t_rows) : 0;
+  const long long mr = (long long)m * r;
+  const long long need = (long long)std::max(nblk, 1) * mr * (long long)sizeof(float);
+  if (need > (long long)PSGD_NOALLOC_SCRATCH_BYTES)
+    return fail("psgd_q_from_mt_noalloc: %lld x %lld at r = %d needs %lld bytes of scratch (%d row blocks x m x r x 4), "
+                "the built-in array holds %lld; use psgd_q_from_mt with a caller-provided workspace instead",
+                (long long)n, (long long)m, r, need, std::max(nblk, 1), (long long)PSGD_NOALLOC_SCRATCH_BYTES);
+
+  CU(cudaSetDevice(device));
+  if (!g_noalloc_ready[device].load(std::memory_order_acquire)) {
+    // set-up, once per device and with that device current: the name of a __device__ array is only a
+    // host-side stand-in, the kernels need the address the runtime reports for it
+    float* ptr = nullptr;
+    CU(cudaGetSymbolAddress((void**)&ptr, g_noalloc_scratch));
+    if (!ptr) return fail("psgd_q_from_mt_noalloc: cudaGetSymbolAddress returned a null address");
+    g_noalloc_ptr[device] = ptr;
+    g_noalloc_ready[device].store(true, std::memory_order_release);
+  }
+  float* scratch = g_noalloc_ptr[device];
+  cudaStream_t s = (cudaStream_t)stream;
+
+  if (n == 0) {  // empty sum: Q = 0
+    k_q_reduce_single<<<(unsigned)((mr + kThreads - 1) / kThreads), kThreads, 0, s>>>(scratch, q_out, mr, 0);
+    return check_launch("k_q_reduce_single");
+  }
+
+  const int R = pow2_ceil(r);
+  const int cpt = (m % 4 == 0) ? 4 : 1;
+  const long long groups = m / cpt;
+  int cgw = 1;
+  while (cgw * 2 <= 128 && groups % (cgw * 2) == 0) cgw *= 2;
+  if (cgw < 16) cgw = (int)std::min<long long>(128, pow2_ceil(groups));
+  const int ncol = (int)((groups + cgw - 1) / cgw);
+  const int RL = kThreads / cgw;
+  const size_t smem = ((size_t)t_rows * R + (size_t)RL * cpt * R * (cgw + 1)) * sizeof(float);
+  const int vec_ok = (cpt == 4 && ((uintptr_t)mat & 15) == 0) ? 1 : 0;
+  const unsigned grid = (unsigned)nblk * (unsigned)ncol;
+  DISPATCH_R(R, {
+    if (set_smem(k_q_from_mt_single<RR>, smem)) return 1;
+    k_q_from_mt_single<RR><<<grid, kThreads, smem, s>>>(mat, p_hat, scratch, (int)n, (int)m, r, cgw, cpt, t_rows, ncol, vec_ok);
+  });
+  if (check_launch("k_q_from_mt_single")) return 1;
+  k_q_reduce_single<<<(unsigned)((mr + kThreads - 1) / kThreads), kThreads, 0, s>>>(scratch, q_out, mr, nblk);
+  return check_launch("k_q_reduce_single");
+}
+
