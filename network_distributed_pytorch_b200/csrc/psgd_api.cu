@@ -307,7 +307,7 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
 
   const long long t1_bytes = env_ll("PSGD_T1_BYTES", 128 * 1024);
   const long long t4_bytes = env_ll("PSGD_T4_BYTES", 96 * 1024);
-  const long long t3_bytes = env_ll("PSGD_T3_BYTES", 128 * 1024);
+  const long long t3_bytes = env_ll("PSGD_T3_BYTES", 256 * 1024);
   const long long t3_maxblk = env_ll("PSGD_T3_MAXBLK", 48);
   const int cgw_cap = (int)env_ll("PSGD_T3_CGW", 128);
 
@@ -368,6 +368,21 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
           t.blk = b;
           p->tiles3.push_back(t);
         }
+  }
+  if (env_ll("PSGD_K3_REVERSE", 1) != 0) {
+    // K1 walks the matrices in index order with the largest one last; K3 walks the same bytes backwards so
+    // that what K1 read last (still in the 126 MB L2) is what K3 reads first, and K4 (K1's order again) starts
+    // on what K3 read last.  M is read three times per step; this turns part of passes two and three into L2 hits.
+    int big = -1;
+    for (int i = 0; i < n_mat; ++i)
+      if (p->mats[i].n && p->mats[i].m &&
+          (big < 0 || (long long)p->mats[i].n * p->mats[i].m > (long long)p->mats[big].n * p->mats[big].m)) big = i;
+    std::vector<ColTile> ordered;
+    ordered.reserve(p->tiles3.size());
+    for (const ColTile& t : p->tiles3) if (t.mat != big) ordered.push_back(t);
+    for (const ColTile& t : p->tiles3) if (t.mat == big) ordered.push_back(t);
+    std::reverse(ordered.begin(), ordered.end());
+    p->tiles3.swap(ordered);
   }
   p->p_total = po;
   p->q_total = qo;

@@ -422,7 +422,7 @@ k_orthogonalize_one(float* __restrict__ mat, int n, int r) {
 template <int R, int CPT, bool VECLD>
 __device__ __forceinline__ void q_tile(const MatDesc& md, const ColTile& t, const float* __restrict__ M,
                                        const float* __restrict__ P, float* __restrict__ ws, float* smem) {
-  constexpr int U = 8;  // rows in flight per thread
+  constexpr int U = (R <= 4 && CPT == 4) ? 16 : 8;  // rows in flight per thread (16 x 16 B x 512 threads = 128 KB per SM)
   constexpr int NV = CPT * R;
   const int m = md.m, r = md.r, cgw = md.cgw;
   const int RL = kThreads / cgw;

@@ -84,7 +84,8 @@ class PowerSGDReducer(Reducer):
         self.reuse_query = reuse_query
         self.extra_power_iterations = int(extra_power_iterations)
         self._plans = {}
-        self._flat = {}
+        self._flat = None
+        self._p_and_flat = None
 
     def _set_random(self, vector):
         # reducer.py:36-38, verbatim semantics including the global reseed
@@ -102,8 +103,7 @@ class PowerSGDReducer(Reducer):
                 dims.append((n, t.nelement() // n if n else 0))
             plan = self._engine.make_plan(dims, self.rank, [t.nelement() for t in vecs])
             self._plans[key] = plan
-            self._flat[key] = self._engine.empty(max(plan.vec_elems, 1))[: plan.vec_elems]
-        return plan, self._flat[key]
+        return plan
 
     def _check(self, lists):
         for lst in lists:
@@ -134,17 +134,23 @@ class PowerSGDReducer(Reducer):
             raise RuntimeError("torch.cat(): expected a non-empty list of Tensors (no <=1-D tensor to pack)")
         mats = [grad_in[i] for i in mat_idx]
         vecs = [grad_in[i] for i in vec_idx]
-        plan, flat = self._plan_for(grad_in, mats, vecs)
+        plan = self._plan_for(grad_in, mats, vecs)
         world = self.n_workers
         bits_communicated = 0
 
         # reducer.py:68-84
         mem_uninitialized = self.p_memory is None
         if mem_uninitialized:
-            self.p_memory = self._engine.empty(plan.p_elems)
+            # P and the flat <=1-D buffer share one allocation (P first, both with their upstream layouts), so
+            # that their two SUM all-reduces (reducer.py:126, :132) go out as a single collective
+            self._p_and_flat = self._engine.empty(plan.p_elems + plan.vec_elems)
+            self.p_memory = self._p_and_flat[: plan.p_elems]
+            self._flat = self._p_and_flat[plan.p_elems :]
             self.q_memory = self._engine.empty(plan.q_elems)
-        elif self.p_memory.nelement() != plan.p_elems or self.q_memory.nelement() != plan.q_elems:
+        elif (self.p_memory.nelement() != plan.p_elems or self.q_memory.nelement() != plan.q_elems
+              or self._flat.nelement() != plan.vec_elems):
             raise RuntimeError("gradient shapes changed after p_memory/q_memory were allocated")
+        flat = self._flat
 
         # reducer.py:101-111
         if not (self.reuse_query and not mem_uninitialized):
@@ -157,12 +163,9 @@ class PowerSGDReducer(Reducer):
                       [fuse_g[i] for i in mat_idx] if fuse_g is not None else None,
                       [fuse_e[i] for i in mat_idx] if fuse_e is not None else None)
 
-        # [For Rank 1] the flat buffer does not depend on P: pack and start its all-reduce first
-        # (upstream starts it after step 4, reducer.py:131-133; the sum is the same)
+        # [For Rank 1] pack the flat buffer now; it travels with P in one collective below
+        # (upstream starts its own async all-reduce after step 4, reducer.py:131-133; the sums are the same)
         plan.pack_vec(flat)
-        rank1_handler = None
-        if world > 1:
-            rank1_handler = torch.distributed.all_reduce(flat, async_op=True)
         bits_communicated += 8 * flat.nelement() * flat.element_size()
 
         for it in range(self.extra_power_iterations + 1):
@@ -170,7 +173,7 @@ class PowerSGDReducer(Reducer):
             plan.p_from_m(self.p_memory, self.q_memory, fuse_add=(fuse_g is not None and it == 0),
                           q_div=(world if it > 0 else 1.0))
             # Step 4 (reducer.py:126-128) ALL_REDUCE_MEAN(P); the divide is folded into step 5
-            all_reduce(self.p_memory)
+            all_reduce(self._p_and_flat if it == 0 else self.p_memory)
             bits_communicated += n_bits(self.p_memory)
             # Step 5 (reducer.py:136-137) P_hat <- ORTHOGONALIZE(P / n_workers)
             plan.orthogonalize(self.p_memory, world)
@@ -184,8 +187,6 @@ class PowerSGDReducer(Reducer):
         plan.finalize(self.p_memory, self.q_memory, world)
 
         # [For Rank 1] (reducer.py:166-168) wait, mean, scatter; q_memory becomes the mean in place
-        if rank1_handler is not None:
-            rank1_handler.wait()
         plan.finish(flat, self.q_memory if world > 1 else None, world)
         return bits_communicated
 

@@ -1,0 +1,68 @@
+"""Two real GPUs over NCCL (skipped on a single-GPU box): the CUDA reducer on two ranks must reproduce what two
+ranks of the upstream reducer produced (golden world-2 fixtures), and both ranks must end with identical P, Q
+and grad_out."""
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+WORKER = r'''
+import os, sys
+import numpy as np, torch, torch.distributed as dist
+sys.path.insert(0, os.environ["PSGD_ROOT"])
+from tests.helpers import Golden, flatten, per_tensor_mem_err, per_tensor_rel_err, rel_err, unflatten
+from network_distributed_pytorch_b200.reducer import PowerSGDReducer
+rank = int(os.environ["RANK"]); local = int(os.environ["LOCAL_RANK"])
+torch.cuda.set_device(local); dev = torch.device("cuda", local)
+dist.init_process_group("nccl", device_id=dev)
+TOL = 1e-5
+for name in ("w2_r2_reuse", "w2_r3_fresh"):
+    g = Golden(name)
+    red = PowerSGDReducer(g.seed, dev, 0, g.reuse, g.rank)
+    assert red.n_workers == 2
+    state = {"buf": None, "off": 0}
+    def fake(vector, red=red, state=state):
+        red.rng.randint(1_000_000_000)
+        k = vector.nelement()
+        vector.data[:] = state["buf"][state["off"]:state["off"] + k].view(vector.shape)
+        state["off"] += k
+    red._set_random = fake
+    mem = [torch.zeros(s, device=dev) for s in g.shapes]
+    for step in range(g.steps):
+        state["buf"] = torch.from_numpy(g.get(0, step, "qinit")).to(dev); state["off"] = 0
+        gin = unflatten(g.get(rank, step, "in"), g.shapes, device=dev)
+        gout = [torch.zeros(s, device=dev) for s in g.shapes]
+        bits = red.reduce(gin, gout, mem)
+        torch.cuda.synchronize()
+        assert bits == int(g.get(0, step, "bits"))
+        assert rel_err(red.p_memory.cpu().numpy(), g.get(0, step, "p")) < TOL
+        assert rel_err(red.q_memory.cpu().numpy(), g.get(0, step, "q")) < TOL
+        assert max(per_tensor_rel_err(flatten(gout), g.get(rank, step, "out"), g.shapes)) < TOL
+        assert max(per_tensor_mem_err(flatten(mem), g.get(rank, step, "mem"), g.get(rank, step, "in"), g.shapes)) < TOL
+        # identical across ranks after the all-reduces
+        for t in (red.p_memory, red.q_memory, torch.cat([x.reshape(-1) for x in gout])):
+            both = [torch.empty_like(t) for _ in range(2)]
+            dist.all_gather(both, t.contiguous())
+            assert torch.equal(both[0], both[1])
+        for t, ref in zip(mem, unflatten(g.get(rank, step, "mem"), g.shapes, device=dev)):
+            t.copy_(ref)
+dist.destroy_process_group()
+print("rank", rank, "ok")
+'''
+
+
+@pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
+def test_two_gpus_match_two_rank_reference(tmp_path):
+    script = tmp_path / "worker.py"
+    script.write_text(WORKER)
+    env = dict(os.environ, PSGD_ROOT=ROOT)
+    out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
+                          "--master-addr", "127.0.0.1", "--master-port", "29533", str(script)],
+                         env=env, capture_output=True, text=True, timeout=600)
+    assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
+    assert out.stdout.count("ok") == 2
