@@ -301,6 +301,25 @@ def run_b200(args):
             clocks["window"] = "1.5 s probe of the same steps right after the timed region"
     barrier()
 
+    # ---- diagnostic: the same step with the caller's error-feedback add fused (reduce_fused) ----------
+    fused_ms = None
+    if not args.no_phase_timing:
+        send = padded_views(torch.zeros(total, device=dev), shapes)
+        for _ in range(3):
+            red.reduce_fused(gin, mem, send)
+        f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        barrier()
+        f0.record()
+        for _ in range(min(K, 20)):
+            red.reduce_fused(gin, mem, send)
+        f1.record()
+        barrier()
+        fused_ms = f0.elapsed_time(f1) / min(K, 20)
+        # restore the state the later legs expect (gin was overwritten with decompressed gradients)
+        in_flat.normal_(generator=gen)
+        mem_flat.zero_()
+        barrier()
+
     # ---- e2e: gradients start in pinned host memory, grad_out is read back ------------------------
     # Three streams and two device buffer sets: the H2D copy of step k+1 and the D2H copy of step k-1 run on
     # the two copy engines while step k reduces, exactly as a host-resident caller would pipeline the
@@ -413,6 +432,9 @@ def run_b200(args):
         "clocks": clocks, "phases": phase_report,
         "phases_note": "per-phase event brackets measured in a separate pass (they add ~13 % to the step); "
                        "only finalize is bracketed inside the timed region",
+        "reduce_fused_ms_per_step": fused_ms,
+        "reduce_fused_note": "reduce_fused(grads, memories, send): ddp_init.py:155-157 (send = g + e, 2 launches per "
+                             "parameter upstream) folded into the P = M Q kernel; 2 more HBM streams than reduce()",
         "host_issue_us_per_step": round(host_us, 1),
         "algorithmic_GBps": world * st["algo_bytes"] / (ms_per_step * 1e-3) / 1e9,
         "hbm_roofline_frac_whole_step": st["algo_bytes"] / (ms_per_step * 1e-3) / 1e9 / peak,

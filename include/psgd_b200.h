@@ -79,8 +79,18 @@ int psgd_set_ptrs(psgd_plan* plan, const void* const* mat_in, void* const* mat_o
                   void* const* mat_mem, const void* const* vec_in, void* const* vec_out,
                   const void* const* grad, const void* const* err, psgd_stream stream);
 
+/* Same as psgd_set_ptrs for a step whose error-feedback add is fused (ddp_init.py:155-157,
+ * send = grad + err for every parameter): mat_send / vec_send are the caller's send buffers (written by
+ * psgd_p_from_m(fuse_add=1) and psgd_pack_vec_fused), grad / err the two operands for matrices and vectors. */
+int psgd_set_ptrs_fused(psgd_plan* plan, const void* const* mat_send, void* const* mat_out,
+                        void* const* mat_mem, const void* const* vec_send, void* const* vec_out,
+                        const void* const* mat_grad, const void* const* mat_err,
+                        const void* const* vec_grad, const void* const* vec_err, psgd_stream stream);
+
 /* K6a: flat = cat(vec_in)             (tensor_buffer.py:19, reducer.py:131) */
 int psgd_pack_vec(psgd_plan* plan, float* flat, psgd_stream stream);
+/* K6a with ddp_init.py:155-157 fused for the <=1-D tensors: vec_send = vec_grad + vec_err, flat = cat(vec_send) */
+int psgd_pack_vec_fused(psgd_plan* plan, float* flat, psgd_stream stream);
 /* K1: P_i = M_i Q_i for every matrix  (reducer.py:121-123).  fuse_add != 0 first forms
  * M = grad + err (ddp_init.py:155-157) and stores it to mat_in.  q_div divides Q while it
  * is staged (1 for the normal path; the worker count when Q still holds an all-reduce

@@ -30,7 +30,9 @@ SIGNATURES = {
     "psgd_tile_count": (ctypes.c_int, [vp, ctypes.c_int]),
     "psgd_tile_get": (ctypes.c_int, [vp, ctypes.c_int, ctypes.c_int, c_i32p]),
     "psgd_set_ptrs": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, vp]),
+    "psgd_set_ptrs_fused": (ctypes.c_int, [vp, vp, vp, vp, vp, vp, vp, vp, vp, vp, vp]),
     "psgd_pack_vec": (ctypes.c_int, [vp, vp, vp]),
+    "psgd_pack_vec_fused": (ctypes.c_int, [vp, vp, vp]),
     "psgd_p_from_m": (ctypes.c_int, [vp, vp, vp, ctypes.c_int, ctypes.c_float, vp]),
     "psgd_orthogonalize": (ctypes.c_int, [vp, vp, ctypes.c_float, vp]),
     "psgd_q_from_mt": (ctypes.c_int, [vp, vp, vp, vp, vp]),

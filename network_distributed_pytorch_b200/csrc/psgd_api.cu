@@ -75,7 +75,7 @@ struct psgd_plan {
   size_t smem1 = 0, smem3 = 0, smem4 = 0;
   // streamed (bulk-copy ring) path for K1 / K4
   bool stream_ok = false;              // static: smem configuration valid and something qualifies
-  bool stream1_now = false, stream4_now = false;  // per step: every qualifying matrix is 16-byte aligned
+  bool stream1_now = false, stream4_now = false, stream1f_now = false;  // per step: every qualifying matrix is 16-byte aligned
   std::vector<char> eligible;
   std::vector<StreamTask> tasks1, tasks4;
   std::vector<int4> tiles1_fb, tiles4_fb;  // direct-load tiles of the matrices that do not qualify
@@ -87,7 +87,7 @@ struct psgd_plan {
   int4* d_tiles4_fb = nullptr;
   int stream_grid = 148, ring_slot_bytes = 0, ring_slots = 0, q_bytes = 0;
   size_t stream_smem = 0;
-  bool attr1_set = false, attr4_set = false;  // opt-in shared memory size set on the streamed kernels
+  bool attr1_set = false, attr1f_set = false, attr4_set = false;  // opt-in shared memory size set on the streamed kernels
   // device tables
   MatDesc* d_mats = nullptr;
   int4* d_tiles1 = nullptr;
@@ -103,7 +103,7 @@ struct psgd_plan {
   bool slot_used[kSlots] = {};
   int cur = -1;
   PtrSlot slot{};
-  bool have_ge = false;
+  bool have_ge = false, have_vge = false;
   // timing
   unsigned timing = 0;  // bit k set: phase k is bracketed by events
   std::vector<Timer> timers;
@@ -494,7 +494,7 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
     rc |= upload(&p->d_orth_tall, p->orth_tall);
     rc |= upload(&p->d_orth_generic, p->orth_generic);
     // ring slot: 5 pointer arrays + flags per matrix, 2 pointer arrays per vector
-    size_t sb = (size_t)n_mat * (5 * sizeof(void*) + sizeof(unsigned)) + (size_t)n_vec * 2 * sizeof(void*);
+    size_t sb = (size_t)n_mat * (5 * sizeof(void*) + sizeof(unsigned)) + (size_t)n_vec * 4 * sizeof(void*);
     sb = (sb + 255) & ~(size_t)255;
     if (sb == 0) sb = 256;
     p->slot_bytes = sb;
@@ -583,9 +583,10 @@ int psgd_tile_get(const psgd_plan* p, int phase, int idx, int32_t* o) {
   return 0;
 }
 
-int psgd_set_ptrs(psgd_plan* p, const void* const* mat_in, void* const* mat_out, void* const* mat_mem,
-                  const void* const* vec_in, void* const* vec_out, const void* const* grad,
-                  const void* const* err, psgd_stream stream) {
+static int set_ptrs_impl(psgd_plan* p, const void* const* mat_in, void* const* mat_out, void* const* mat_mem,
+                         const void* const* vec_in, void* const* vec_out, const void* const* grad,
+                         const void* const* err, const void* const* vec_grad, const void* const* vec_err,
+                         psgd_stream stream) {
   if (need_device(p)) return 1;
   if (p->n_mat && (!mat_in || !mat_out || !mat_mem)) return fail("psgd_set_ptrs: null matrix pointer array");
   if (p->n_vec && (!vec_in || !vec_out)) return fail("psgd_set_ptrs: null vector pointer array");
@@ -603,10 +604,13 @@ int psgd_set_ptrs(psgd_plan* p, const void* const* mat_in, void* const* mat_out,
   const void** h_e = (const void**)(h + 4 * L * 8);
   const void** h_vin = (const void**)(h + 5 * L * 8);
   void** h_vout = (void**)(h + 5 * L * 8 + L1 * 8);
-  unsigned* h_fl = (unsigned*)(h + 5 * L * 8 + 2 * L1 * 8);
-  const size_t used_bytes = 5 * L * 8 + 2 * L1 * 8 + L * 4;
+  const void** h_vg = (const void**)(h + 5 * L * 8 + 2 * L1 * 8);
+  const void** h_ve = (const void**)(h + 5 * L * 8 + 3 * L1 * 8);
+  unsigned* h_fl = (unsigned*)(h + 5 * L * 8 + 4 * L1 * 8);
+  const size_t used_bytes = 5 * L * 8 + 4 * L1 * 8 + L * 4;
   p->have_ge = grad && err;
-  bool s1 = p->stream_ok, s4 = p->stream_ok;
+  p->have_vge = vec_grad && vec_err;
+  bool s1 = p->stream_ok, s4 = p->stream_ok, s1f = p->stream_ok && grad && err;
   for (size_t i = 0; i < L; ++i) {
     const MatDesc& md = p->mats[i];
     const bool nonempty = md.n && md.m;
@@ -626,16 +630,21 @@ int psgd_set_ptrs(psgd_plan* p, const void* const* mat_in, void* const* mat_out,
     h_fl[i] = fl;
     if (p->stream_ok && p->eligible[i]) {
       if (!(fl & kFlagInVec)) s1 = false;
+      if (!(fl & kFlagInVec) || !(fl & kFlagGeVec)) s1f = false;
       if (!(fl & kFlagInVec) || !(fl & kFlagOutVec)) s4 = false;
     }
   }
   p->stream1_now = s1;
+  p->stream1f_now = s1f;
   p->stream4_now = s4;
   for (size_t j = 0; j < L1; ++j) {
     const bool nonempty = p->v_pre[j + 1] > p->v_pre[j];
     if (nonempty && (!vec_in[j] || !vec_out[j])) return fail("psgd_set_ptrs: vector %zu has a null pointer", j);
     h_vin[j] = vec_in[j];
     h_vout[j] = vec_out[j];
+    h_vg[j] = p->have_vge ? vec_grad[j] : nullptr;
+    h_ve[j] = p->have_vge ? vec_err[j] : nullptr;
+    if (p->have_vge && nonempty && (!vec_grad[j] || !vec_err[j])) return fail("psgd_set_ptrs: vector %zu has a null grad/err pointer", j);
   }
   if (p->cur >= 0 && memcmp(h, p->h_ring + (size_t)p->cur * p->slot_bytes, used_bytes) == 0) {
     return 0;  // same addresses as the table already on the device: nothing to upload
@@ -651,8 +660,37 @@ int psgd_set_ptrs(psgd_plan* p, const void* const* mat_in, void* const* mat_out,
   p->slot.e = (const float* const*)(d + 4 * L * 8);
   p->slot.vin = (const float* const*)(d + 5 * L * 8);
   p->slot.vout = (float* const*)(d + 5 * L * 8 + L1 * 8);
-  p->slot.flags = (const unsigned*)(d + 5 * L * 8 + 2 * L1 * 8);
+  p->slot.vg = (const float* const*)(d + 5 * L * 8 + 2 * L1 * 8);
+  p->slot.ve = (const float* const*)(d + 5 * L * 8 + 3 * L1 * 8);
+  p->slot.flags = (const unsigned*)(d + 5 * L * 8 + 4 * L1 * 8);
   return 0;
+}
+
+int psgd_set_ptrs(psgd_plan* p, const void* const* mat_in, void* const* mat_out, void* const* mat_mem,
+                  const void* const* vec_in, void* const* vec_out, const void* const* grad,
+                  const void* const* err, psgd_stream stream) {
+  return set_ptrs_impl(p, mat_in, mat_out, mat_mem, vec_in, vec_out, grad, err, nullptr, nullptr, stream);
+}
+
+int psgd_set_ptrs_fused(psgd_plan* p, const void* const* mat_send, void* const* mat_out, void* const* mat_mem,
+                        const void* const* vec_send, void* const* vec_out, const void* const* mat_grad,
+                        const void* const* mat_err, const void* const* vec_grad, const void* const* vec_err,
+                        psgd_stream stream) {
+  if (p && ((p->n_mat && (!mat_grad || !mat_err)) || (p->n_vec && (!vec_grad || !vec_err))))
+    return fail("psgd_set_ptrs_fused: grad / err pointer arrays are required");
+  return set_ptrs_impl(p, mat_send, mat_out, mat_mem, vec_send, vec_out, mat_grad, mat_err, vec_grad, vec_err, stream);
+}
+
+int psgd_pack_vec_fused(psgd_plan* p, float* flat, psgd_stream stream) {
+  if (need_device(p) || need_ptrs(p)) return 1;
+  if (!p->have_vge) return fail("psgd_pack_vec_fused: call psgd_set_ptrs_fused first");
+  if (p->v_total == 0) return 0;
+  if (!flat) return fail("psgd_pack_vec_fused: flat is null");
+  CU(cudaSetDevice(p->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  PhaseScope ts(p, PSGD_PHASE_PACK, s);
+  k_gather_sum<<<(unsigned)p->vtiles.size(), kThreads, 0, s>>>(p->d_vtiles, p->slot, flat);
+  return check_launch("k_gather_sum");
 }
 
 int psgd_pack_vec(psgd_plan* p, float* flat, psgd_stream stream) {
@@ -707,20 +745,31 @@ int psgd_p_from_m(psgd_plan* p, float* p_mem, const float* q_mem, int fuse_add, 
   const DevPlan dp = dev_plan(p);
   const unsigned grid = (unsigned)p->tiles1.size();
   PhaseScope ts(p, PSGD_PHASE_P_FROM_M, s);
-  if (!fuse_add && p->stream1_now) {
+  if (fuse_add ? p->stream1f_now : p->stream1_now) {
     StreamPlan sp{p->d_tasks1, p->d_counters, (int)p->tasks1.size(), p->ring_slot_bytes, p->ring_slots, p->q_bytes, p->d_dbg};
     DISPATCH_R(p->R, {
-      if (!p->attr1_set) CU(cudaFuncSetAttribute((const void*)k_p_from_m_stream<RR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->stream_smem));
-      p->attr1_set = true;
-      k_p_from_m_stream<RR><<<p->stream_grid, kStreamThreads, p->stream_smem, s>>>(dp, p->slot, sp, q_mem, p_mem, q_div);
+      if (fuse_add) {
+        if (!p->attr1f_set) CU(cudaFuncSetAttribute((const void*)k_p_from_m_stream<RR, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->stream_smem));
+        p->attr1f_set = true;
+        k_p_from_m_stream<RR, true><<<p->stream_grid, kStreamThreads, p->stream_smem, s>>>(dp, p->slot, sp, q_mem, p_mem, q_div);
+      } else {
+        if (!p->attr1_set) CU(cudaFuncSetAttribute((const void*)k_p_from_m_stream<RR, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->stream_smem));
+        p->attr1_set = true;
+        k_p_from_m_stream<RR, false><<<p->stream_grid, kStreamThreads, p->stream_smem, s>>>(dp, p->slot, sp, q_mem, p_mem, q_div);
+      }
     });
     if (check_launch("k_p_from_m_stream")) return 1;
     if (!p->tiles1_fb.empty()) {
       DevPlan fb = dp;
       fb.tiles1 = p->d_tiles1_fb;
       DISPATCH_R(p->R, {
-        if (set_smem(k_p_from_m<RR, false>, p->smem1)) return 1;
-        k_p_from_m<RR, false><<<(unsigned)p->tiles1_fb.size(), kThreads, p->smem1, s>>>(fb, p->slot, q_mem, p_mem, q_div);
+        if (fuse_add) {
+          if (set_smem(k_p_from_m<RR, true>, p->smem1)) return 1;
+          k_p_from_m<RR, true><<<(unsigned)p->tiles1_fb.size(), kThreads, p->smem1, s>>>(fb, p->slot, q_mem, p_mem, q_div);
+        } else {
+          if (set_smem(k_p_from_m<RR, false>, p->smem1)) return 1;
+          k_p_from_m<RR, false><<<(unsigned)p->tiles1_fb.size(), kThreads, p->smem1, s>>>(fb, p->slot, q_mem, p_mem, q_div);
+        }
       });
       if (check_launch("k_p_from_m")) return 1;
     }

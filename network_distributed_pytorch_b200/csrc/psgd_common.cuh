@@ -54,6 +54,8 @@ struct PtrSlot {
   const unsigned* flags;    // alignment flags per matrix
   const float* const* vin;  // <=1-D inputs
   float* const* vout;       // <=1-D outputs
+  const float* const* vg;   // <=1-D raw gradients (fuse_add)
+  const float* const* ve;   // <=1-D error memories (fuse_add)
 };
 
 enum : unsigned {

@@ -696,6 +696,22 @@ k_scatter(const VecTile* __restrict__ tiles, const T* __restrict__ flat, void* c
   for (int i = threadIdx.x; i < t.count; i += kThreads) d[i] = s[i];
 }
 
+// K6a with the caller's error-feedback add fused (ddp_init.py:155-157 for the <=1-D tensors):
+// send = grad + err is stored to the send buffer AND to the flat buffer in one pass
+__global__ void __launch_bounds__(kThreads)
+k_gather_sum(const VecTile* __restrict__ tiles, PtrSlot ps, float* __restrict__ flat) {
+  const VecTile t = tiles[blockIdx.x];
+  const float* g = ps.vg[t.tensor] + t.start;
+  const float* e = ps.ve[t.tensor] + t.start;
+  float* send = const_cast<float*>(ps.vin[t.tensor]) + t.start;
+  float* d = flat + t.flat_off;
+  for (int i = threadIdx.x; i < t.count; i += kThreads) {
+    const float v = g[i] + e[i];
+    send[i] = v;
+    d[i] = v;
+  }
+}
+
 // K6b: vec_out = flat / n_workers (reducer.py:167-168); blocks past the vector tiles scale q_mem in place
 // (q_mem /= n_workers, reducer.py:147)
 __global__ void __launch_bounds__(kThreads)

@@ -103,10 +103,11 @@ struct StreamSmem {
   uint64_t* empty;  // all consumer warps are done with the slot
   uint64_t* desc;   // the slot's descriptor is published (well before its data lands)
   volatile int4* slot_desc;
-  struct MatInfo { const float* base; const float* q; int m; int r; long long pad; };
+  struct MatInfo { const float* base; const float* q; const float* g; const float* e; int m; int r; long long pad; };
   MatInfo* matinfo;
 };
-constexpr int kStreamSmemExtra = 3 * kMaxSlots * 8 + kMaxSlots * 16 + kMatCache * 32;
+constexpr int kStreamSmemExtra = 3 * kMaxSlots * 8 + kMaxSlots * 16 + kMatCache * 48;
+static_assert(sizeof(StreamSmem::MatInfo) == 48, "MatInfo layout");
 
 __device__ __forceinline__ StreamSmem carve(unsigned char* base, const StreamPlan& sp) {
   StreamSmem s;
@@ -127,6 +128,8 @@ __device__ __forceinline__ StreamSmem::MatInfo mat_info(const DevPlan& pl, const
   const MatDesc md = pl.mats[mat];
   mi.base = ps.in[mat];
   mi.q = q_mem + md.q_off;
+  mi.g = ps.g[mat];
+  mi.e = ps.e[mat];
   mi.m = md.m;
   mi.r = md.r;
   mi.pad = 0;
@@ -148,6 +151,8 @@ __device__ __forceinline__ void stream_setup(const DevPlan& pl, const PtrSlot& p
     const MatDesc md = pl.mats[i];
     sm.matinfo[i].base = ps.in[i];
     sm.matinfo[i].q = q_mem + md.q_off;
+    sm.matinfo[i].g = ps.g[i];
+    sm.matinfo[i].e = ps.e[i];
     sm.matinfo[i].m = md.m;
     sm.matinfo[i].r = md.r;
   }
@@ -157,7 +162,7 @@ __device__ __forceinline__ void stream_setup(const DevPlan& pl, const PtrSlot& p
 // The producer: one thread takes tasks from the global counter, cuts them into units and refills slots
 // as the consumers release them.  Nothing on its per-unit path touches global memory: the task after
 // the current one is requested while the current one streams.
-template <int ROWS>
+template <int ROWS, bool FUSE = false>
 __device__ __forceinline__ void stream_producer(const DevPlan& pl, const PtrSlot& ps, const StreamPlan& sp,
                                                 const StreamSmem& sm, const float* q_mem) {
   int it = 0;
@@ -189,7 +194,8 @@ __device__ __forceinline__ void stream_producer(const DevPlan& pl, const PtrSlot
       }
       prev_mat = task.mat;
     }
-    const int rpu = max(1, sp.slot_bytes / (m * 4));
+    // FUSE: a unit carries the rows of grad and, right behind them, the same rows of err
+    const int rpu = max(1, sp.slot_bytes / (m * 4 * (FUSE ? 2 : 1)));
     const int sub_per_unit = (rpu + ROWS - 1) / ROWS;
     int rot = task.rot0;
     for (int row0 = task.row_begin; row0 < task.row_end; row0 += rpu, ++it) {
@@ -201,8 +207,14 @@ __device__ __forceinline__ void stream_producer(const DevPlan& pl, const PtrSlot
       sm.slot_desc[slot].x = task.mat; sm.slot_desc[slot].y = row0;
       sm.slot_desc[slot].z = nrows; sm.slot_desc[slot].w = rot;
       mbar_arrive(&sm.desc[slot]);
-      mbar_arrive_expect_tx(&sm.full[slot], bytes);
-      bulk_g2s(sm.ring + (size_t)slot * sp.slot_bytes, mi.base + (size_t)row0 * m, bytes, &sm.full[slot]);
+      if (FUSE) {
+        mbar_arrive_expect_tx(&sm.full[slot], 2u * bytes);
+        bulk_g2s(sm.ring + (size_t)slot * sp.slot_bytes, mi.g + (size_t)row0 * m, bytes, &sm.full[slot]);
+        bulk_g2s(sm.ring + (size_t)slot * sp.slot_bytes + bytes, mi.e + (size_t)row0 * m, bytes, &sm.full[slot]);
+      } else {
+        mbar_arrive_expect_tx(&sm.full[slot], bytes);
+        bulk_g2s(sm.ring + (size_t)slot * sp.slot_bytes, mi.base + (size_t)row0 * m, bytes, &sm.full[slot]);
+      }
       rot = (rot + sub_per_unit) % kConsumerWarps;
     }
     t = t_next;
@@ -259,9 +271,10 @@ __device__ __forceinline__ void consume_q_unit(float* Qs, const float* slot, con
 }
 
 // =======================================================================================
-// K1 (streamed):  P = M Q
+// K1 (streamed):  P = M Q ; with FUSE the caller's M = grad + err (ddp_init.py:155-157) is formed on the way:
+// both operands arrive in the slot, the sum is stored to the send buffer and fed to the FMAs
 // =======================================================================================
-template <int R>
+template <int R, bool FUSE>
 __global__ void __launch_bounds__(kStreamThreads, 1)
 k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict__ q_mem, float* __restrict__ p_mem,
                   float q_div) {
@@ -273,12 +286,13 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
   stream_setup(pl, ps, sp, sm, q_mem);
 
   if (warp == kConsumerWarps) {
-    if (lane == 0) stream_producer<ROWS>(pl, ps, sp, sm, q_mem);
+    if (lane == 0) stream_producer<ROWS, FUSE>(pl, ps, sp, sm, q_mem);
     return;
   }
 
   int cur_mat = -1, m = 0, r = 0, pitch = 0;
   float* P = nullptr;
+  float* Mw = nullptr;  // FUSE: the send buffer M is written to
   const bool dbg = sp.dbg != nullptr && threadIdx.x == 0;
   unsigned long long d_t0 = 0, d_desc = 0, d_data = 0, d_q = 0, d_units = 0, d_sw = 0, d_work = 0;
   long long c0 = 0, c_begin = 0;
@@ -298,6 +312,7 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
       const StreamSmem::MatInfo mi = mat_info(pl, ps, sm, q_mem, u_mat);
       if (u_mat != cur_mat) {
         P = p_mem + pl.mats[u_mat].p_off;  // in flight while the Q data lands
+        Mw = const_cast<float*>(mi.base);
         m = mi.m; r = mi.r; pitch = q_pitch(m, R);
         cur_mat = u_mat;
         consumer_sync();  // everyone is done with the previous matrix' Q
@@ -338,6 +353,14 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
         float4 x[ROWS];
 #pragma unroll
         for (int a = 0; a < ROWS; ++a) x[a] = *reinterpret_cast<const float4*>(rowp[a] + 4 * k);
+        if (FUSE) {
+#pragma unroll
+          for (int a = 0; a < ROWS; ++a) {
+            const float4 e = *reinterpret_cast<const float4*>(rowp[a] + (size_t)u_n * m + 4 * k);
+            x[a].x += e.x; x[a].y += e.y; x[a].z += e.z; x[a].w += e.w;
+            if (a < nr) st_stream4(Mw + (size_t)(u_a + rbase + a) * m + 4 * k, x[a]);
+          }
+        }
 #pragma unroll
         for (int c = 0; c < R; ++c) {
           const float4 q = *reinterpret_cast<const float4*>(sm.qs + c * pitch + 4 * k);

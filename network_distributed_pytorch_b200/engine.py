@@ -65,7 +65,12 @@ class CudaPlan:
         return out
 
     # -- per step ---------------------------------------------------------------------------
-    def set_ptrs(self, mat_in, mat_out, mat_mem, vec_in, vec_out, grad=None, err=None):
+    def set_ptrs(self, mat_in, mat_out, mat_mem, vec_in, vec_out, grad=None, err=None, vec_grad=None, vec_err=None):
+        if vec_grad is not None:  # fused error-feedback add: operands for matrices and vectors
+            arrays = (_ptrs(mat_in), _ptrs(mat_out), _ptrs(mat_mem), _ptrs(vec_in), _ptrs(vec_out),
+                      _ptrs(grad), _ptrs(err), _ptrs(vec_grad), _ptrs(vec_err))
+            _lib.check(self._lib.psgd_set_ptrs_fused(self._h, *arrays, _stream(self.device)), self._lib)
+            return
         arrays = (_ptrs(mat_in), _ptrs(mat_out), _ptrs(mat_mem), _ptrs(vec_in), _ptrs(vec_out),
                   _ptrs(grad) if grad is not None else None, _ptrs(err) if err is not None else None)
         _lib.check(self._lib.psgd_set_ptrs(self._h, *arrays, _stream(self.device)), self._lib)
@@ -77,6 +82,9 @@ class CudaPlan:
 
     def pack_vec(self, flat):
         _lib.check(self._lib.psgd_pack_vec(self._h, flat.data_ptr(), _stream(self.device)), self._lib)
+
+    def pack_vec_fused(self, flat):
+        _lib.check(self._lib.psgd_pack_vec_fused(self._h, flat.data_ptr(), _stream(self.device)), self._lib)
 
     def p_from_m(self, p_mem, q_mem, fuse_add=False, q_div=1.0):
         _lib.check(self._lib.psgd_p_from_m(self._h, p_mem.data_ptr(), q_mem.data_ptr(), int(fuse_add),

@@ -122,6 +122,19 @@ class PowerSGDReducer(Reducer):
         """
         return self._reduce(grad_in, grad_out, memory_out, None, None)
 
+    def reduce_fused(self, grads, memories, send_buffers):
+        """The caller's error-feedback add fused into the reduction (no upstream counterpart as one call):
+
+            for g, e, s in zip(grads, memories, send_buffers): s[:] = g + e      # ddp_init.py:155-157
+            return self.reduce(send_buffers, grads, memories)                    # ddp_init.py:161
+
+        with the add formed inside the P = M Q kernel (matrices) and the flat-buffer gather (<=1-D tensors)
+        instead of two launches per parameter.  ``grads`` ends up holding the decompressed mean gradient,
+        ``memories`` the new local error, ``send_buffers`` g + e -- exactly as after the two upstream lines."""
+        if not (len(grads) == len(memories) == len(send_buffers)):
+            raise ValueError("grads, memories and send_buffers must have the same length")
+        return self._reduce(send_buffers, grads, memories, grads, memories)
+
     def _reduce(self, grad_in, grad_out, memory_out, fuse_g, fuse_e):
         if not (len(grad_in) == len(grad_out) == len(memory_out)):
             raise ValueError("grad_in, grad_out and memory_out must have the same length")
@@ -158,19 +171,27 @@ class PowerSGDReducer(Reducer):
                 q = self.q_memory[info["q_off"] : info["q_off"] + info["m"] * info["r"]].view(info["m"], info["r"])
                 self._set_random(q)
 
-        plan.set_ptrs(mats, [grad_out[i] for i in mat_idx], [memory_out[i] for i in mat_idx],
-                      vecs, [grad_out[i] for i in vec_idx],
-                      [fuse_g[i] for i in mat_idx] if fuse_g is not None else None,
-                      [fuse_e[i] for i in mat_idx] if fuse_e is not None else None)
+        fused = fuse_g is not None
+        if fused:
+            plan.set_ptrs(mats, [grad_out[i] for i in mat_idx], [memory_out[i] for i in mat_idx],
+                          vecs, [grad_out[i] for i in vec_idx],
+                          [fuse_g[i] for i in mat_idx], [fuse_e[i] for i in mat_idx],
+                          [fuse_g[i] for i in vec_idx], [fuse_e[i] for i in vec_idx])
+        else:
+            plan.set_ptrs(mats, [grad_out[i] for i in mat_idx], [memory_out[i] for i in mat_idx],
+                          vecs, [grad_out[i] for i in vec_idx])
 
         # [For Rank 1] pack the flat buffer now; it travels with P in one collective below
         # (upstream starts its own async all-reduce after step 4, reducer.py:131-133; the sums are the same)
-        plan.pack_vec(flat)
+        if fused:
+            plan.pack_vec_fused(flat)
+        else:
+            plan.pack_vec(flat)
         bits_communicated += 8 * flat.nelement() * flat.element_size()
 
         for it in range(self.extra_power_iterations + 1):
             # Step 3 (reducer.py:121-123) P <- M Q
-            plan.p_from_m(self.p_memory, self.q_memory, fuse_add=(fuse_g is not None and it == 0),
+            plan.p_from_m(self.p_memory, self.q_memory, fuse_add=(fused and it == 0),
                           q_div=(world if it > 0 else 1.0))
             # Step 4 (reducer.py:126-128) ALL_REDUCE_MEAN(P); the divide is folded into step 5
             all_reduce(self._p_and_flat if it == 0 else self.p_memory)

@@ -31,10 +31,17 @@ class OraclePlan:
             q = q_mem[d["q_off"] : d["q_off"] + d["m"] * d["r"]].view(d["m"], d["r"]) if q_mem is not None else None
             yield i, d, p, q
 
-    def set_ptrs(self, mat_in, mat_out, mat_mem, vec_in, vec_out, grad=None, err=None):
+    def set_ptrs(self, mat_in, mat_out, mat_mem, vec_in, vec_out, grad=None, err=None, vec_grad=None, vec_err=None):
         self.calls.append("set_ptrs")
         self.mat_in, self.mat_out, self.mat_mem = mat_in, mat_out, mat_mem
         self.vec_in, self.vec_out, self.grad, self.err = vec_in, vec_out, grad, err
+        self.vec_grad, self.vec_err = vec_grad, vec_err
+
+    def pack_vec_fused(self, flat):
+        self.calls.append("pack_vec_fused")
+        for s, g, e in zip(self.vec_in, self.vec_grad, self.vec_err):
+            s[:] = g + e
+        flat[:] = torch.cat([t.reshape(-1) for t in self.vec_in])
 
     def pack_vec(self, flat):
         self.calls.append("pack_vec")

@@ -222,6 +222,36 @@ def test_full_size_distilbert_properties():
     assert all(torch.equal(a, b) for a, b in zip(gout, gout2)) and all(torch.equal(a, b) for a, b in zip(mem, mem2))
 
 
+@pytest.mark.parametrize("setname", ["transformer_slice", "odd_columns", "wide_chunked"])
+def test_reduce_fused_matches_add_then_reduce(setname):
+    """reduce_fused(grads, memories, send) == (send = g + e; reduce(send, grads, memories)) on the GPU, both
+    through the streamed kernels (aligned transformer shapes) and the direct ones (odd / wide shapes)."""
+    from network_distributed_pytorch_b200.reducer import PowerSGDReducer
+
+    dev = torch.device("cuda", 0)
+    shapes = SHAPE_SETS[setname]
+    gen = torch.Generator(device=dev).manual_seed(77)
+    g = [torch.randn(s, device=dev, generator=gen) for s in shapes]
+    e = [torch.randn(s, device=dev, generator=gen) * 0.1 for s in shapes]
+    a = PowerSGDReducer(714, dev, 0, True, 4)
+    send_a = [x + y for x, y in zip(g, e)]
+    ga, ea = [t.clone() for t in g], [t.clone() for t in e]
+    bits_a = a.reduce(send_a, ga, ea)
+    b = PowerSGDReducer(714, dev, 0, True, 4)
+    gb, eb, send_b = [t.clone() for t in g], [t.clone() for t in e], [torch.zeros(s, device=dev) for s in shapes]
+    bits_b = b.reduce_fused(gb, eb, send_b)
+    torch.cuda.synchronize()
+    assert bits_a == bits_b
+    for x, y in zip(send_a, send_b):
+        assert torch.equal(x, y)  # the add itself is exact
+    assert rel_err(b.p_memory.cpu().numpy(), a.p_memory.cpu().numpy()) < TOL
+    assert rel_err(b.q_memory.cpu().numpy(), a.q_memory.cpu().numpy()) < TOL
+    errs = per_tensor_rel_err(flatten(gb), flatten(ga), shapes)
+    assert max(errs) < TOL, errs
+    errs = per_tensor_mem_err(flatten(eb), flatten(ea), flatten(send_a), shapes)
+    assert max(errs) < TOL, errs
+
+
 def test_fused_add_entry_point():
     """psgd_p_from_m(fuse_add=1): M = grad + err is formed inside K1 and stored to mat_in."""
     from network_distributed_pytorch_b200.engine import CudaEngine

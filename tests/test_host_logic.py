@@ -122,6 +122,24 @@ def test_extra_power_iterations_match_oracle():
     assert rel_err(flatten(o1), flatten(o2)) < 1e-6 and rel_err(flatten(m1), flatten(m2)) < 1e-6
 
 
+def test_reduce_fused_equals_add_then_reduce():
+    torch.manual_seed(11)
+    shapes = [(12, 20), (5,), (6, 2, 3), (7,)]
+    g = [torch.randn(s) for s in shapes]
+    e = [torch.randn(s) for s in shapes]
+    # upstream order: send = g + e ; reduce(send, grads, memories)
+    a = make(rank=2)
+    send_a = [x + y for x, y in zip(g, e)]
+    ga, ea = [t.clone() for t in g], [t.clone() for t in e]
+    bits_a = a.reduce(send_a, ga, ea)
+    b = make(rank=2)
+    gb, eb, send_b = [t.clone() for t in g], [t.clone() for t in e], [torch.zeros(s) for s in shapes]
+    bits_b = b.reduce_fused(gb, eb, send_b)
+    assert bits_a == bits_b
+    for x, y in zip(ga + ea + send_a, gb + eb + send_b):
+        assert torch.equal(x, y)
+
+
 def test_module_helpers():
     assert R.n_bits(torch.zeros(10)) == 320
     assert R.all_reduce(torch.zeros(1)) is None  # world 1: skipped (reducer.py:193-195)
