@@ -44,6 +44,8 @@ def parse():
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--no-phase-timing", action="store_true")
     ap.add_argument("--no-clock-probe", action="store_true", help="profiling runs: skip the 1.5 s clock probe")
+    ap.add_argument("--skip-train", action="store_true", help="skip the training samples/sec leg")
+    ap.add_argument("--train-steps", type=int, default=8)
     return ap.parse_args()
 
 
@@ -375,6 +377,33 @@ def run_b200(args):
                "steps": E, "h2d_bytes_per_step": total * 4, "d2h_bytes_per_step": total * 4,
                "path": "per step: pinned host -> HBM copy of all gradients, PowerSGDReducer.reduce(), grad_out HBM -> "
                        "pinned host; copies of neighbouring steps overlap on the two copy engines"}
+    # ---- training samples/sec (BASELINE.json metric, second half): the upstream loop on synthetic tokens ----
+    training = None
+    if not args.skip_train and args.workload in ("distilbert", "bert-large", "resnet18", "resnet50"):
+        try:
+            from network_distributed_pytorch_b200 import harness
+
+            del in_flat, out_flat, mem_flat, gin, gout, mem
+            torch.cuda.empty_cache()
+            training = {}
+            seq = 512 if args.workload in ("distilbert", "bert-large") else 224
+            bsz = 16 if args.workload in ("distilbert", "bert-large") else 256
+            for loop in ("upstream", "fused"):
+                res = harness.measure_samples_per_sec(
+                    args.workload, lambda: PowerSGDReducer(714, dev, 0, True, args.rank), dev, batch=bsz, seq_len=seq,
+                    steps=args.train_steps, warmup=3, loop=loop, world=world, barrier=barrier)
+                tms = torch.tensor([res["ms_per_step"]], device=dev)
+                if world > 1:
+                    dist.all_reduce(tms, op=dist.ReduceOp.MAX)
+                res["ms_per_step"] = float(tms.item())
+                res["samples_per_sec"] = world * bsz / (res["ms_per_step"] * 1e-3)
+                training[loop] = res
+            training["note"] = ("random-init model of the named architecture, random tokens, bf16 autocast forward/backward, "
+                                "fp32 parameters and reducer; 'upstream' = the reference loop with this reducer dropped in, "
+                                "'fused' = same arithmetic through reduce_fused + FusedMomentumSGD")
+        except Exception as exc:  # the headline metric must not depend on this leg
+            training = {"unavailable": f"{type(exc).__name__}: {exc}"[:300]}
+
     if sampler:
         sampler.stop()
 
@@ -432,6 +461,7 @@ def run_b200(args):
         "clocks": clocks, "phases": phase_report,
         "phases_note": "per-phase event brackets measured in a separate pass (they add ~13 % to the step); "
                        "only finalize is bracketed inside the timed region",
+        "training": training,
         "reduce_fused_ms_per_step": fused_ms,
         "reduce_fused_note": "reduce_fused(grads, memories, send): ddp_init.py:155-157 (send = g + e, 2 launches per "
                              "parameter upstream) folded into the P = M Q kernel; 2 more HBM streams than reduce()",

@@ -31,6 +31,7 @@ extern "C" {
 
 typedef struct psgd_plan psgd_plan;
 typedef struct psgd_tb psgd_tb;
+typedef struct psgd_sgd psgd_sgd;
 typedef void* psgd_stream;
 
 #define PSGD_ABI_VERSION 1
@@ -131,6 +132,14 @@ int psgd_tb_create(int n, const int64_t* nelem, int elem_size, int device, psgd_
 int psgd_tb_destroy(psgd_tb* tb);
 int psgd_tb_pack(psgd_tb* tb, const void* const* src, void* flat, psgd_stream stream);
 int psgd_tb_unpack(psgd_tb* tb, const void* flat, void* const* dst, psgd_stream stream);
+
+/* The caller-side update that follows reduce() upstream (ddp_init.py:166-178), over all parameters in one
+ * launch instead of four per parameter:  m = first_step ? g : momentum * m + g ;  g += m ;  p -= lr * g.
+ * nelem: element counts of the parameters; params / grads / momenta: host arrays of fp32 device pointers. */
+int psgd_sgd_create(int n, const int64_t* nelem, int device, psgd_sgd** out);
+int psgd_sgd_destroy(psgd_sgd* h);
+int psgd_sgd_step(psgd_sgd* h, void* const* params, void* const* grads, void* const* momenta, float lr,
+                  float momentum, int first_step, psgd_stream stream);
 
 /* In-place modified Gram-Schmidt of one n x r row-major matrix: the module-level
  * orthogonalize(matrix) of reducer.py:180-191. */

@@ -46,6 +46,9 @@ SIGNATURES = {
     "psgd_tb_destroy": (ctypes.c_int, [vp]),
     "psgd_tb_pack": (ctypes.c_int, [vp, vp, vp, vp]),
     "psgd_tb_unpack": (ctypes.c_int, [vp, vp, vp, vp]),
+    "psgd_sgd_create": (ctypes.c_int, [ctypes.c_int, c_i64p, ctypes.c_int, ctypes.POINTER(vp)]),
+    "psgd_sgd_destroy": (ctypes.c_int, [vp]),
+    "psgd_sgd_step": (ctypes.c_int, [vp, vp, vp, vp, ctypes.c_float, ctypes.c_float, ctypes.c_int, vp]),
     "psgd_orthogonalize_one": (ctypes.c_int, [vp, ctypes.c_int64, ctypes.c_int, ctypes.c_int, vp]),
     "psgd_q_from_mt_noalloc": (ctypes.c_int, [vp, vp, vp, ctypes.c_int64, ctypes.c_int64, ctypes.c_int, ctypes.c_int, vp]),
 }

@@ -1061,6 +1061,103 @@ int psgd_tb_unpack(psgd_tb* tb, const void* flat, void* const* dst, psgd_stream 
   return check_launch("k_scatter");
 }
 
+// ---- fused momentum + SGD step (the caller-side loops after reduce(), ddp_init.py:166-178) ---------------
+
+struct psgd_sgd {
+  int device = -1;
+  int n = 0;
+  std::vector<VecTile> tiles;
+  VecTile* d_tiles = nullptr;
+  size_t slot_bytes = 0;
+  char* h_ring = nullptr;
+  char* d_ring = nullptr;
+  cudaEvent_t slot_ev[kSlots] = {};
+  bool slot_used[kSlots] = {};
+  int cur = -1;
+};
+
+int psgd_sgd_create(int n, const int64_t* nelem, int device, psgd_sgd** out) {
+  if (!out) return fail("out is null");
+  *out = nullptr;
+  if (n < 0 || (n && !nelem)) return fail("psgd_sgd_create: bad tensor list");
+  if (device < 0) return fail("psgd_sgd_create: needs a CUDA device");
+  psgd_sgd* h = new psgd_sgd();
+  h->device = device;
+  h->n = n;
+  for (int i = 0; i < n; ++i) {
+    if (nelem[i] < 0 || nelem[i] > 0x7fffffffLL) { delete h; return fail("psgd_sgd_create: unsupported length"); }
+    for (long long st = 0; st < nelem[i]; st += kEwTileElems) {
+      VecTile vt;
+      vt.flat_off = 0;
+      vt.tensor = i;
+      vt.start = (int)st;
+      vt.count = (int)std::min<long long>(kEwTileElems, nelem[i] - st);
+      vt.pad_ = 0;
+      h->tiles.push_back(vt);
+    }
+  }
+  h->slot_bytes = std::max<size_t>(256, ((size_t)n * 3 * 8 + 255) & ~(size_t)255);
+  int rc = 0;
+  if (cudaSetDevice(device) != cudaSuccess) rc = fail("cudaSetDevice(%d) failed", device);
+  if (!rc) rc = upload(&h->d_tiles, h->tiles);
+  if (!rc && cudaMallocHost((void**)&h->h_ring, h->slot_bytes * kSlots) != cudaSuccess) rc = fail("cudaMallocHost failed");
+  if (!rc && cudaMalloc((void**)&h->d_ring, h->slot_bytes * kSlots) != cudaSuccess) rc = fail("cudaMalloc failed");
+  for (int s = 0; s < kSlots && !rc; ++s)
+    if (cudaEventCreateWithFlags(&h->slot_ev[s], cudaEventDisableTiming) != cudaSuccess) rc = fail("cudaEventCreate failed");
+  if (rc) {
+    std::string keep = g_err;
+    psgd_sgd_destroy(h);
+    g_err = keep;
+    return 1;
+  }
+  *out = h;
+  return 0;
+}
+
+int psgd_sgd_destroy(psgd_sgd* h) {
+  if (!h) return 0;
+  cudaSetDevice(h->device);
+  cudaFree(h->d_tiles);
+  cudaFree(h->d_ring);
+  if (h->h_ring) cudaFreeHost(h->h_ring);
+  for (int s = 0; s < kSlots; ++s)
+    if (h->slot_ev[s]) cudaEventDestroy(h->slot_ev[s]);
+  delete h;
+  return 0;
+}
+
+int psgd_sgd_step(psgd_sgd* h, void* const* params, void* const* grads, void* const* momenta, float lr,
+                  float momentum, int first_step, psgd_stream stream) {
+  if (!h) return fail("null handle");
+  if (h->tiles.empty()) return 0;
+  if (!params || !grads || !momenta) return fail("psgd_sgd_step: null pointer array");
+  CU(cudaSetDevice(h->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  const int slot = (h->cur + 1) % kSlots;
+  if (h->slot_used[slot]) CU(cudaEventSynchronize(h->slot_ev[slot]));
+  char* hp = h->h_ring + (size_t)slot * h->slot_bytes;
+  char* dp = h->d_ring + (size_t)slot * h->slot_bytes;
+  const size_t n = h->n;
+  for (size_t i = 0; i < n; ++i) {
+    if (!params[i] || !grads[i] || !momenta[i]) return fail("psgd_sgd_step: tensor %zu has a null pointer", i);
+    if (((uintptr_t)params[i] | (uintptr_t)grads[i] | (uintptr_t)momenta[i]) & 3) return fail("psgd_sgd_step: tensor %zu is not 4-byte aligned", i);
+    ((void**)hp)[i] = params[i];
+    ((void**)hp)[n + i] = grads[i];
+    ((void**)hp)[2 * n + i] = momenta[i];
+  }
+  if (h->cur < 0 || memcmp(hp, h->h_ring + (size_t)h->cur * h->slot_bytes, 3 * n * 8) != 0) {
+    CU(cudaMemcpyAsync(dp, hp, 3 * n * 8, cudaMemcpyHostToDevice, s));
+    CU(cudaEventRecord(h->slot_ev[slot], s));
+    h->slot_used[slot] = true;
+    h->cur = slot;
+  } else {
+    dp = h->d_ring + (size_t)h->cur * h->slot_bytes;
+  }
+  float* const* d = (float* const*)dp;
+  k_momentum_step<<<(unsigned)h->tiles.size(), kThreads, 0, s>>>(h->d_tiles, d, d + n, d + 2 * n, lr, momentum, first_step);
+  return check_launch("k_momentum_step");
+}
+
 int psgd_orthogonalize_one(float* mat, int64_t n, int r, int device, psgd_stream stream) {
   if (n < 0 || r < 0) return fail("psgd_orthogonalize_one: negative shape");
   if (n == 0 || r == 0) return 0;

@@ -735,4 +735,53 @@ k_finish(DevPlan pl, PtrSlot ps, const float* __restrict__ flat, int n_vtiles, f
   }
 }
 
+// =======================================================================================
+// Caller-side update that follows reduce() upstream (ddp_init.py:166-178), one sweep instead of four
+// launches per parameter:   m = first ? g : lambda * m + g ;  g += m ;  p -= lr * g
+// Tile = up to kEwTileElems elements of one tensor; 128-bit accesses when the three tensors allow it.
+// =======================================================================================
+constexpr int kEwTileElems = 4096;
+
+__global__ void __launch_bounds__(kThreads)
+k_momentum_step(const VecTile* __restrict__ tiles, float* const* __restrict__ params, float* const* __restrict__ grads,
+                float* const* __restrict__ momenta, float lr, float lambda, int first) {
+  const VecTile t = tiles[blockIdx.x];
+  float* p = params[t.tensor] + t.start;
+  float* g = grads[t.tensor] + t.start;
+  float* m = momenta[t.tensor] + t.start;
+  const bool vec = (((uintptr_t)p | (uintptr_t)g | (uintptr_t)m) & 15) == 0;
+  if (vec) {
+    const int n4 = t.count >> 2;
+    for (int i = threadIdx.x; i < n4; i += kThreads) {
+      float4 gv = reinterpret_cast<float4*>(g)[i];
+      float4 pv = reinterpret_cast<float4*>(p)[i];
+      float4 mv;
+      if (first) {
+        mv = gv;
+      } else {
+        mv = reinterpret_cast<float4*>(m)[i];
+        mv.x = fmaf(lambda, mv.x, gv.x); mv.y = fmaf(lambda, mv.y, gv.y);
+        mv.z = fmaf(lambda, mv.z, gv.z); mv.w = fmaf(lambda, mv.w, gv.w);
+      }
+      gv.x += mv.x; gv.y += mv.y; gv.z += mv.z; gv.w += mv.w;
+      pv.x = fmaf(-lr, gv.x, pv.x); pv.y = fmaf(-lr, gv.y, pv.y);
+      pv.z = fmaf(-lr, gv.z, pv.z); pv.w = fmaf(-lr, gv.w, pv.w);
+      reinterpret_cast<float4*>(m)[i] = mv;
+      reinterpret_cast<float4*>(g)[i] = gv;
+      reinterpret_cast<float4*>(p)[i] = pv;
+    }
+    for (int i = (n4 << 2) + threadIdx.x; i < t.count; i += kThreads) {
+      const float mv = first ? g[i] : fmaf(lambda, m[i], g[i]);
+      const float gv = g[i] + mv;
+      m[i] = mv; g[i] = gv; p[i] = fmaf(-lr, gv, p[i]);
+    }
+  } else {
+    for (int i = threadIdx.x; i < t.count; i += kThreads) {
+      const float mv = first ? g[i] : fmaf(lambda, m[i], g[i]);
+      const float gv = g[i] + mv;
+      m[i] = mv; g[i] = gv; p[i] = fmaf(-lr, gv, p[i]);
+    }
+  }
+}
+
 }  // namespace psgd
