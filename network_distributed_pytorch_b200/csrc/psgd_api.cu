@@ -169,17 +169,18 @@ void build_row_tiles(const psgd_plan* p, std::vector<int4>& out, long long targe
 // one matrix (one Q stage per CTA).
 void build_stream_tasks(const psgd_plan* p, int rows_per_sub, std::vector<StreamTask>& tasks) {
   tasks.clear();
+  // smallest matrices first, largest last: the long head tasks cover the many small matrices (one Q stage
+  // each), the fine-grained tail of the schedule walks through the few largest ones
   std::vector<int> order;
-  int big = -1;
   long long total = 0;
   for (int i = 0; i < p->n_mat; ++i) {
     if (!p->eligible[i]) continue;
     total += (long long)p->mats[i].n * p->mats[i].m * 4;
-    if (big < 0 || (long long)p->mats[i].n * p->mats[i].m > (long long)p->mats[big].n * p->mats[big].m) big = i;
+    order.push_back(i);
   }
-  for (int i = 0; i < p->n_mat; ++i)
-    if (p->eligible[i] && i != big) order.push_back(i);
-  if (big >= 0) order.push_back(big);
+  std::stable_sort(order.begin(), order.end(), [&](int a, int b) {
+    return (long long)p->mats[a].n * p->mats[a].m < (long long)p->mats[b].n * p->mats[b].m;
+  });
 
   const long long div = 2LL * p->stream_grid * env_ll("PSGD_GSS_DIV", 1);
   const long long min_units = std::max<long long>(1, env_ll("PSGD_GSS_MIN_UNITS", 2));

@@ -272,8 +272,9 @@ __device__ __forceinline__ void orth_body(float* __restrict__ P, int n, int r, f
 template <int R, int RPT>
 __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r, float world,
                                             int crank, int csize) {
-  __shared__ float wsum[32][R];
-  __shared__ float part[2][kOrthCluster][R];
+  constexpr int LPV = 32 / R;  // lanes per value after a warp_fold<R>
+  __shared__ __align__(16) float wsum[32][R];
+  __shared__ __align__(16) float part[2][kOrthCluster][R];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nthr = blockDim.x, nwarp = nthr >> 5;
   const int per = (n + csize - 1) / csize;
@@ -282,15 +283,18 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
 
   // IEEE fp32 division costs ~40 instructions; one reciprocal per scale factor and multiplies instead
   // (exact for power-of-two worker counts, otherwise within 1 ulp of the reference's true division)
-  const bool vec4 = (R == 4) && (r == 4) && ((reinterpret_cast<uintptr_t>(P) & 15) == 0);
+  const bool vec4 = (R % 4 == 0) && (r == R) && ((reinterpret_cast<uintptr_t>(P) & 15) == 0);
   float v[RPT][R];
 #pragma unroll
   for (int k = 0; k < RPT; ++k) {
     const int row = lo + tid + k * nthr;
     if (vec4) {
-      float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-      if (row < hi) t = *reinterpret_cast<const float4*>(P + (size_t)row * 4);
-      v[k][0] = t.x; v[k][1 % R] = t.y; v[k][2 % R] = t.z; v[k][3 % R] = t.w;
+#pragma unroll
+      for (int c = 0; c < R; c += 4) {
+        float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (row < hi) t = *reinterpret_cast<const float4*>(P + (size_t)row * R + c);
+        v[k][c] = t.x; v[k][(c + 1) % R] = t.y; v[k][(c + 2) % R] = t.z; v[k][(c + 3) % R] = t.w;
+      }
     } else {
 #pragma unroll
       for (int j = 0; j < R; ++j) v[k][j] = (row < hi && j < r) ? P[(size_t)row * r + j] : 0.f;
@@ -307,6 +311,7 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
 #pragma unroll
   for (int i = 0; i < R; ++i) {
     if (i < r) {  // uniform over the CTA / cluster
+      // partial sums of col_i . col_j for j >= i (j < i stays 0); one butterfly fold reduces all R of them
       float s[R];
 #pragma unroll
       for (int j = 0; j < R; ++j) s[j] = 0.f;
@@ -314,38 +319,44 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
       for (int k = 0; k < RPT; ++k)
 #pragma unroll
         for (int j = i; j < R; ++j) s[j] = fmaf(v[k][i], v[k][j], s[j]);
-#pragma unroll
-      for (int j = i; j < R; ++j) {
-        if (j < r) {
-          const float w = warp_sum(s[j]);
-          if (lane == 0) wsum[warp][j] = w;
-        }
+      {
+        const float w = warp_fold<R>(s, lane);
+        if ((lane % LPV) == 0) wsum[warp][lane / LPV] = w;
       }
       __syncthreads();
       const int par = i & 1;
       if (warp == 0) {
+        float t[R];
 #pragma unroll
-        for (int j = i; j < R; ++j) {
-          if (j < r) {
-            const float t = warp_sum(lane < nwarp ? wsum[lane][j] : 0.f);
-            if (csize > 1) {
-              if (lane < csize) {
-                float* remote = cg::this_cluster().map_shared_rank(&part[0][0][0], lane);
-                remote[(par * kOrthCluster + crank) * R + j] = t;
-              }
-            } else if (lane == 0) {
-              part[par][0][j] = t;
+        for (int j = 0; j < R; ++j) t[j] = (lane < nwarp) ? wsum[lane][j] : 0.f;
+        const float w = warp_fold<R>(t, lane);
+        if ((lane % LPV) == 0) {
+          const int j = lane / LPV;
+          if (csize > 1) {
+            for (int dst = 0; dst < csize; ++dst) {
+              float* remote = cg::this_cluster().map_shared_rank(&part[0][0][0], dst);
+              remote[(par * kOrthCluster + crank) * R + j] = w;
             }
+          } else {
+            part[par][0][j] = w;
           }
         }
       }
       if (csize > 1) cg::this_cluster().sync(); else __syncthreads();
       float tot[R];
 #pragma unroll
-      for (int j = i; j < R; ++j) {
-        tot[j] = 0.f;
-        if (j < r)
-          for (int c = 0; c < csize; ++c) tot[j] += part[par][c][j];
+      for (int j = 0; j < R; ++j) tot[j] = 0.f;
+      for (int c = 0; c < csize; ++c) {
+        if (R % 4 == 0) {
+#pragma unroll
+          for (int j = 0; j < R; j += 4) {
+            const float4 q = *reinterpret_cast<const float4*>(&part[par][c][j]);
+            tot[j] += q.x; tot[(j + 1) % R] += q.y; tot[(j + 2) % R] += q.z; tot[(j + 3) % R] += q.w;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < R; ++j) tot[j] += part[par][c][j];
+        }
       }
       const float inv = 1.0f / (sqrtf(tot[i]) + 1e-8f);  // eps outside the root, reducer.py:186
       float coef[R];
@@ -356,8 +367,7 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
         const float vi = v[k][i] * inv;
         v[k][i] = vi;
 #pragma unroll
-        for (int j = i + 1; j < R; ++j)
-          if (j < r) v[k][j] = fmaf(-coef[j], vi, v[k][j]);
+        for (int j = i + 1; j < R; ++j) v[k][j] = fmaf(-coef[j], vi, v[k][j]);
       }
     }
   }
@@ -366,7 +376,10 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
     const int row = lo + tid + k * nthr;
     if (row < hi) {
       if (vec4) {
-        *reinterpret_cast<float4*>(P + (size_t)row * 4) = make_float4(v[k][0], v[k][1 % R], v[k][2 % R], v[k][3 % R]);
+#pragma unroll
+        for (int c = 0; c < R; c += 4)
+          *reinterpret_cast<float4*>(P + (size_t)row * R + c) =
+              make_float4(v[k][c], v[k][(c + 1) % R], v[k][(c + 2) % R], v[k][(c + 3) % R]);
       } else {
 #pragma unroll
         for (int j = 0; j < R; ++j)

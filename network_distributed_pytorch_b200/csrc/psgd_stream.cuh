@@ -443,16 +443,25 @@ k_finalize_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
       if (lane == 0) mbar_arrive(&sm.empty[slot]);
       continue;
     }
+    // Work items of a unit = (group of ROWS rows) x (column slice).  Wide matrices give few rows per unit, so
+    // the rows alone would keep one or two warps busy; this kernel has no reduction, so the columns are simply
+    // cut into `cs` slices until all eight warps have an item.
     const int nsub = (u_n + ROWS - 1) / ROWS;
+    int cs = 1;
+    while (nsub * cs < kConsumerWarps && cs < 8) cs <<= 1;
+    const int nitems = nsub * cs;
     const int j0 = (warp - u_w % kConsumerWarps + kConsumerWarps) % kConsumerWarps;
-    if (j0 >= nsub) {  // see k_p_from_m_stream
+    if (j0 >= nitems) {  // see k_p_from_m_stream
       if (lane == 0) mbar_arrive(&sm.empty[slot]);
       continue;
     }
     const int kmax = m >> 2;
+    const int kslice = (kmax + cs - 1) / cs;
     bool landed = false;
-    for (int j = j0; j < nsub; j += kConsumerWarps) {
-      const int rbase = j * ROWS;
+    for (int j = j0; j < nitems; j += kConsumerWarps) {
+      const int rbase = (j / cs) * ROWS;
+      const int k_lo = (j % cs) * kslice;
+      const int k_hi = (k_lo + kslice < kmax) ? k_lo + kslice : kmax;
       const int nr = (u_n - rbase < ROWS) ? (u_n - rbase) : ROWS;
       float p[ROWS][R];  // the P rows do not live in the slot: request them before waiting for M
 #pragma unroll
@@ -466,7 +475,7 @@ k_finalize_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
         landed = true;
       }
 #pragma unroll 2
-      for (int k = lane; k < kmax; k += 32) {
+      for (int k = k_lo + lane; k < k_hi; k += 32) {
         float4 q[R];
 #pragma unroll
         for (int c = 0; c < R; ++c) q[c] = *reinterpret_cast<const float4*>(sm.qs + c * pitch + 4 * k);

@@ -84,6 +84,7 @@ class PowerSGDReducer(Reducer):
         self.reuse_query = reuse_query
         self.extra_power_iterations = int(extra_power_iterations)
         self._plans = {}
+        self._call_cache = None
         self._flat = None
         self._p_and_flat = None
 
@@ -138,48 +139,59 @@ class PowerSGDReducer(Reducer):
     def _reduce(self, grad_in, grad_out, memory_out, fuse_g, fuse_e):
         if not (len(grad_in) == len(grad_out) == len(memory_out)):
             raise ValueError("grad_in, grad_out and memory_out must have the same length")
-        self._check((grad_in, grad_out, memory_out))
-        # reducer.py:53-62
-        vec_idx = [i for i, t in enumerate(grad_in) if t.ndimension() <= 1]
-        mat_idx = [i for i, t in enumerate(grad_in) if t.ndimension() > 1]
-        if not vec_idx:
-            # upstream: TensorBuffer([]) -> torch.cat of an empty list (tensor_buffer.py:19)
-            raise RuntimeError("torch.cat(): expected a non-empty list of Tensors (no <=1-D tensor to pack)")
-        mats = [grad_in[i] for i in mat_idx]
-        vecs = [grad_in[i] for i in vec_idx]
-        plan = self._plan_for(grad_in, mats, vecs)
+        fused = fuse_g is not None
         world = self.n_workers
         bits_communicated = 0
 
-        # reducer.py:68-84
-        mem_uninitialized = self.p_memory is None
-        if mem_uninitialized:
-            # P and the flat <=1-D buffer share one allocation (P first, both with their upstream layouts), so
-            # that their two SUM all-reduces (reducer.py:126, :132) go out as a single collective
-            self._p_and_flat = self._engine.empty(plan.p_elems + plan.vec_elems)
-            self.p_memory = self._p_and_flat[: plan.p_elems]
-            self._flat = self._p_and_flat[plan.p_elems :]
-            self.q_memory = self._engine.empty(plan.q_elems)
-        elif (self.p_memory.nelement() != plan.p_elems or self.q_memory.nelement() != plan.q_elems
-              or self._flat.nelement() != plan.vec_elems):
-            raise RuntimeError("gradient shapes changed after p_memory/q_memory were allocated")
-        flat = self._flat
-
-        # reducer.py:101-111
-        if not (self.reuse_query and not mem_uninitialized):
-            for info in plan.mats:
-                q = self.q_memory[info["q_off"] : info["q_off"] + info["m"] * info["r"]].view(info["m"], info["r"])
-                self._set_random(q)
-
-        fused = fuse_g is not None
-        if fused:
-            plan.set_ptrs(mats, [grad_out[i] for i in mat_idx], [memory_out[i] for i in mat_idx],
-                          vecs, [grad_out[i] for i in vec_idx],
-                          [fuse_g[i] for i in mat_idx], [fuse_e[i] for i in mat_idx],
-                          [fuse_g[i] for i in vec_idx], [fuse_e[i] for i in vec_idx])
+        # Host fast path: the very same storages as in the previous call (persistent send / grad / memory buffers)
+        # need no re-validation, no list splitting and no pointer upload.  The previous call's tensors are kept
+        # alive in the cache, so an equal address means the same storage, not a recycled one.
+        sig = (fused, tuple([t.data_ptr() for t in grad_in]), tuple([t.data_ptr() for t in grad_out]),
+               tuple([t.data_ptr() for t in memory_out]))
+        cache = self._call_cache
+        if cache is not None and cache[0] == sig and self.reuse_query:
+            plan = cache[1]
         else:
-            plan.set_ptrs(mats, [grad_out[i] for i in mat_idx], [memory_out[i] for i in mat_idx],
-                          vecs, [grad_out[i] for i in vec_idx])
+            self._check((grad_in, grad_out, memory_out))
+            # reducer.py:53-62
+            vec_idx = [i for i, t in enumerate(grad_in) if t.ndimension() <= 1]
+            mat_idx = [i for i, t in enumerate(grad_in) if t.ndimension() > 1]
+            if not vec_idx:
+                # upstream: TensorBuffer([]) -> torch.cat of an empty list (tensor_buffer.py:19)
+                raise RuntimeError("torch.cat(): expected a non-empty list of Tensors (no <=1-D tensor to pack)")
+            mats = [grad_in[i] for i in mat_idx]
+            vecs = [grad_in[i] for i in vec_idx]
+            plan = self._plan_for(grad_in, mats, vecs)
+
+            # reducer.py:68-84
+            mem_uninitialized = self.p_memory is None
+            if mem_uninitialized:
+                # P and the flat <=1-D buffer share one allocation (P first, both with their upstream layouts), so
+                # that their two SUM all-reduces (reducer.py:126, :132) go out as a single collective
+                self._p_and_flat = self._engine.empty(plan.p_elems + plan.vec_elems)
+                self.p_memory = self._p_and_flat[: plan.p_elems]
+                self._flat = self._p_and_flat[plan.p_elems :]
+                self.q_memory = self._engine.empty(plan.q_elems)
+            elif (self.p_memory.nelement() != plan.p_elems or self.q_memory.nelement() != plan.q_elems
+                  or self._flat.nelement() != plan.vec_elems):
+                raise RuntimeError("gradient shapes changed after p_memory/q_memory were allocated")
+
+            # reducer.py:101-111
+            if not (self.reuse_query and not mem_uninitialized):
+                for info in plan.mats:
+                    q = self.q_memory[info["q_off"] : info["q_off"] + info["m"] * info["r"]].view(info["m"], info["r"])
+                    self._set_random(q)
+
+            if fused:
+                plan.set_ptrs(mats, [grad_out[i] for i in mat_idx], [memory_out[i] for i in mat_idx],
+                              vecs, [grad_out[i] for i in vec_idx],
+                              [fuse_g[i] for i in mat_idx], [fuse_e[i] for i in mat_idx],
+                              [fuse_g[i] for i in vec_idx], [fuse_e[i] for i in vec_idx])
+            else:
+                plan.set_ptrs(mats, [grad_out[i] for i in mat_idx], [memory_out[i] for i in mat_idx],
+                              vecs, [grad_out[i] for i in vec_idx])
+            self._call_cache = (sig, plan, list(grad_in), list(grad_out), list(memory_out))
+        flat = self._flat
 
         # [For Rank 1] pack the flat buffer now; it travels with P in one collective below
         # (upstream starts its own async all-reduce after step 4, reducer.py:131-133; the sums are the same)
