@@ -141,6 +141,17 @@ int psgd_sgd_destroy(psgd_sgd* h);
 int psgd_sgd_step(psgd_sgd* h, void* const* params, void* const* grads, void* const* momenta, float lr,
                   float momentum, int first_step, psgd_stream stream);
 
+/* One-shot SUM all-reduce of a small fp32 buffer over peer-mapped memory, replacing dist.all_reduce on the packed
+ * P || flat and Q buffers (reducer.py:126,132,145) inside one NVLink domain.  peer_in[r] / peer_signal[r]: rank r's
+ * input buffer and uint32 signal pad as mapped into THIS process (e.g. torch symmetric memory), world <= 8 entries;
+ * out: local result (must not alias any input); slot0: first of `world` pad slots reserved for this call site;
+ * epoch: a counter the caller increments on every call at this site (same value on all ranks).  Sums are formed in
+ * rank order, so every rank obtains the same bits.  Call sites must alternate between two (buffer, slot0) pairs,
+ * as the reducer's P and Q phases do: that alternation is what guarantees a peer has finished reading an input
+ * before its owner overwrites it. */
+int psgd_peer_allreduce(const void* const* peer_in, void* const* peer_signal, float* out, int64_t n, int rank,
+                        int world, int slot0, uint32_t epoch, int device, psgd_stream stream);
+
 /* In-place modified Gram-Schmidt of one n x r row-major matrix: the module-level
  * orthogonalize(matrix) of reducer.py:180-191. */
 int psgd_orthogonalize_one(float* mat, int64_t n, int r, int device, psgd_stream stream);

@@ -797,4 +797,76 @@ k_momentum_step(const VecTile* __restrict__ tiles, float* const* __restrict__ pa
   }
 }
 
+// =======================================================================================
+// One-shot SUM all-reduce over peer-mapped (symmetric) memory for the two small packed buffers of a step
+// (P || flat: reducer.py:126,132 and Q: reducer.py:145).  Every rank reads all ranks' input buffers over
+// NVLink and adds them in rank order, so all ranks produce bit-identical sums (the property the upstream loop
+// relies on after dist.all_reduce).  The messages are 0.7-8 MB: latency-bound, which is why one kernel with a
+// flag barrier beats a general collective here.
+//   barrier: block 0 publishes "my input is complete" (epoch) into every peer's signal pad, every block waits
+//   until its own pad shows the epoch from every rank.  No trailing barrier is needed: the P and Q phases
+//   alternate, and a rank can only overwrite its P input after it has passed the Q barrier (and vice versa),
+//   which every peer reaches only after it finished reading.
+// =======================================================================================
+constexpr int kMaxPeers = 8;
+struct PeerArgs {
+  const float* in[kMaxPeers];   // input buffer of every rank, mapped into this process
+  unsigned* sig[kMaxPeers];     // signal pad of every rank (uint32 slots), mapped into this process
+};
+
+__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 ld_sys4(const float* p) {
+  float4 v;
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float ld_sys1(const float* p) {
+  float v;
+  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_peer_allreduce(PeerArgs a, float* __restrict__ out, long long n, int rank, int world, int slot0, unsigned epoch) {
+  if (blockIdx.x == 0 && (int)threadIdx.x < world) {
+    __threadfence_system();
+    st_release_sys(a.sig[threadIdx.x] + slot0 + rank, epoch);  // tell peer threadIdx.x: rank's input is ready
+  }
+  if ((int)threadIdx.x < world) {
+    const unsigned* mine = a.sig[rank] + slot0 + threadIdx.x;
+    const long long t0 = clock64();
+    while ((int)(ld_acquire_sys(mine) - epoch) < 0) {
+      // a peer that never arrives (crashed rank) must not hang the GPU: give up after ~10 s and fault loudly
+      if (clock64() - t0 > 20000000000LL) {
+        printf("psgd k_peer_allreduce: rank %d timed out waiting for rank %d (epoch %u)\n", rank, (int)threadIdx.x, epoch);
+        __trap();
+      }
+    }
+  }
+  __syncthreads();
+  const long long n4 = n >> 2;
+  const long long stride = (long long)gridDim.x * kThreads;
+  for (long long i = (long long)blockIdx.x * kThreads + threadIdx.x; i < n4; i += stride) {
+    float4 s = ld_sys4(a.in[0] + 4 * i);
+    for (int r = 1; r < world; ++r) {
+      const float4 v = ld_sys4(a.in[r] + 4 * i);
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    reinterpret_cast<float4*>(out)[i] = s;
+  }
+  for (long long i = (n4 << 2) + (long long)blockIdx.x * kThreads + threadIdx.x; i < n; i += stride) {
+    float s = ld_sys1(a.in[0] + i);
+    for (int r = 1; r < world; ++r) s += ld_sys1(a.in[r] + i);
+    out[i] = s;
+  }
+}
+
 }  // namespace psgd

@@ -1,0 +1,71 @@
+"""Peer-memory exchange for the two packed all-reduces of a step (reducer.py:126,132,145) inside one NVLink domain.
+
+The input buffers of the two phases live in torch symmetric memory (every rank maps every other rank's buffer and
+signal pad); the sum itself is this package's own kernel (psgd_peer_allreduce): each rank reads all ranks' inputs
+and adds them in rank order, so every rank gets the same bits.  Set-up is a collective; if it fails on any rank
+every rank falls back to torch.distributed.all_reduce (NCCL).
+
+Opt-in (PSGD_PEER_ALLREDUCE=1).  Measured on 8 x B200 (DistilBERT r=4 step): 2 GPUs 0.310 ms vs 0.315 ms with NCCL,
+4 GPUs 0.325 vs 0.324, 8 GPUs 0.356 vs 0.346 -- a one-shot pull reads (world-1) x the message, NCCL's in-switch
+reduction wins from 8 ranks on, so NCCL stays the default."""
+import ctypes
+import os
+
+import torch
+import torch.distributed as dist
+
+from . import _lib
+
+_SLOT0 = 256          # first signal-pad slot used by this package (torch's own barrier uses the low slots)
+MAX_WORLD = 8
+
+
+class PeerExchange:
+    def __init__(self, device, n_pf, n_q):
+        import torch.distributed._symmetric_memory as symm
+
+        self.device = device
+        self.world = dist.get_world_size()
+        self.rank = dist.get_rank()
+        self._lib = _lib.load()
+        group = dist.group.WORLD
+        pad4 = lambda n: (max(n, 4) + 3) // 4 * 4
+        self.buf = [symm.empty(pad4(n_pf), dtype=torch.float32, device=device),
+                    symm.empty(pad4(n_q), dtype=torch.float32, device=device)]
+        self.hdl = [symm.rendezvous(b, group) for b in self.buf]
+        for h in self.hdl:
+            if len(h.buffer_ptrs) != self.world or h.signal_pad_size < 4 * (_SLOT0 + MAX_WORLD):
+                raise RuntimeError("unexpected symmetric memory geometry")
+        self._in = [_lib.ptr_array(list(h.buffer_ptrs)) for h in self.hdl]
+        self._sig = [_lib.ptr_array(list(h.signal_pad_ptrs)) for h in self.hdl]
+        self.epoch = [0, 0]
+        for b in self.buf:
+            b.zero_()
+        torch.cuda.synchronize(device)
+        dist.barrier()
+
+    def allreduce(self, which, out, n):
+        """out[:n] = sum over ranks of buf[which][:n]  (which: 0 = P || flat, 1 = Q)."""
+        self.epoch[which] += 1
+        stream = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        _lib.check(self._lib.psgd_peer_allreduce(self._in[which], self._sig[which], out.data_ptr(), n, self.rank,
+                                                 self.world, _SLOT0, self.epoch[which], self.device.index, stream),
+                   self._lib)
+
+
+def try_setup(device, n_pf, n_q):
+    """Collective.  Returns a PeerExchange on every rank, or None on every rank."""
+    world = dist.get_world_size()
+    if (world < 2 or world > MAX_WORLD or device.type != "cuda" or os.environ.get("PSGD_PEER_ALLREDUCE", "0") != "1"
+            or dist.get_backend() != "nccl"):
+        return None
+    ex, ok = None, 1
+    try:
+        ex = PeerExchange(device, n_pf, n_q)
+    except Exception as exc:  # noqa: BLE001 -- any failure means "use NCCL", decided jointly below
+        ok = 0
+        if os.environ.get("PSGD_DEBUG"):
+            print("peer exchange unavailable:", repr(exc))
+    flag = torch.tensor([ok], device=device, dtype=torch.int32)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    return ex if int(flag.item()) == 1 else None

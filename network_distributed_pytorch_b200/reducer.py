@@ -85,6 +85,7 @@ class PowerSGDReducer(Reducer):
         self.extra_power_iterations = int(extra_power_iterations)
         self._plans = {}
         self._call_cache = None
+        self._peer = None
         self._flat = None
         self._p_and_flat = None
 
@@ -172,6 +173,12 @@ class PowerSGDReducer(Reducer):
                 self.p_memory = self._p_and_flat[: plan.p_elems]
                 self._flat = self._p_and_flat[plan.p_elems :]
                 self.q_memory = self._engine.empty(plan.q_elems)
+                # inside one NVLink domain the two all-reduces run as this package's own peer-memory kernel
+                self._peer = None
+                if world > 1 and getattr(self._engine, "name", "") == "cuda-sm100a":
+                    from . import peer
+
+                    self._peer = peer.try_setup(self._engine.device, plan.p_elems + plan.vec_elems, plan.q_elems)
             elif (self.p_memory.nelement() != plan.p_elems or self.q_memory.nelement() != plan.q_elems
                   or self._flat.nelement() != plan.vec_elems):
                 raise RuntimeError("gradient shapes changed after p_memory/q_memory were allocated")
@@ -192,28 +199,40 @@ class PowerSGDReducer(Reducer):
                               vecs, [grad_out[i] for i in vec_idx])
             self._call_cache = (sig, plan, list(grad_in), list(grad_out), list(memory_out))
         flat = self._flat
+        px = self._peer
+        if px is not None:  # phase inputs live in symmetric memory, results land in p_memory || flat and q_memory
+            n_pf = self._p_and_flat.nelement()
+            p_in, flat_in, q_in = px.buf[0][: plan.p_elems], px.buf[0][plan.p_elems : n_pf], px.buf[1][: plan.q_elems]
+        else:
+            p_in, flat_in, q_in = self.p_memory, flat, self.q_memory
 
         # [For Rank 1] pack the flat buffer now; it travels with P in one collective below
         # (upstream starts its own async all-reduce after step 4, reducer.py:131-133; the sums are the same)
         if fused:
-            plan.pack_vec_fused(flat)
+            plan.pack_vec_fused(flat_in)
         else:
-            plan.pack_vec(flat)
+            plan.pack_vec(flat_in)
         bits_communicated += 8 * flat.nelement() * flat.element_size()
 
         for it in range(self.extra_power_iterations + 1):
             # Step 3 (reducer.py:121-123) P <- M Q
-            plan.p_from_m(self.p_memory, self.q_memory, fuse_add=(fused and it == 0),
+            plan.p_from_m(p_in, self.q_memory, fuse_add=(fused and it == 0),
                           q_div=(world if it > 0 else 1.0))
             # Step 4 (reducer.py:126-128) ALL_REDUCE_MEAN(P); the divide is folded into step 5
-            all_reduce(self._p_and_flat if it == 0 else self.p_memory)
+            if px is not None:
+                px.allreduce(0, self._p_and_flat, n_pf)
+            else:
+                all_reduce(self._p_and_flat if it == 0 else self.p_memory)
             bits_communicated += n_bits(self.p_memory)
             # Step 5 (reducer.py:136-137) P_hat <- ORTHOGONALIZE(P / n_workers)
             plan.orthogonalize(self.p_memory, world)
             # Step 6 (reducer.py:140-142) Q <- M^T P_hat
-            plan.q_from_mt(self.p_memory, self.q_memory)
+            plan.q_from_mt(self.p_memory, q_in)
             # Step 7 (reducer.py:145-147) ALL_REDUCE_MEAN(Q); the divide is applied while Q is staged
-            all_reduce(self.q_memory)
+            if px is not None:
+                px.allreduce(1, self.q_memory, plan.q_elems)
+            else:
+                all_reduce(self.q_memory)
             bits_communicated += n_bits(self.q_memory)
 
         # Step 8 + 9 (reducer.py:158-163) decompress and memorise the local error in one sweep

@@ -52,17 +52,20 @@ for name in ("w2_r2_reuse", "w2_r3_fresh"):
         for t, ref in zip(mem, unflatten(g.get(rank, step, "mem"), g.shapes, device=dev)):
             t.copy_(ref)
 dist.destroy_process_group()
-print("rank", rank, "ok")
+print("rank", rank, "ok", "peer=%s" % (red._peer is not None))
 '''
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
-def test_two_gpus_match_two_rank_reference(tmp_path):
+@pytest.mark.parametrize("peer", ["1", "0"])  # own peer-memory all-reduce kernel / torch.distributed (NCCL)
+def test_two_gpus_match_two_rank_reference(tmp_path, peer):
     script = tmp_path / "worker.py"
     script.write_text(WORKER)
-    env = dict(os.environ, PSGD_ROOT=ROOT)
+    env = dict(os.environ, PSGD_ROOT=ROOT, PSGD_PEER_ALLREDUCE=peer, PSGD_DEBUG="1")
     out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
                           "--master-addr", "127.0.0.1", "--master-port", "29533", str(script)],
                          env=env, capture_output=True, text=True, timeout=600)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
     assert out.stdout.count("ok") == 2
+    if peer == "1":
+        assert "peer=True" in out.stdout, out.stdout[-2000:]
