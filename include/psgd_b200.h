@@ -98,6 +98,10 @@ int psgd_pack_vec_fused(psgd_plan* plan, float* flat, psgd_stream stream);
  * SUM, used by extra power iterations). */
 int psgd_p_from_m(psgd_plan* plan, float* p_mem, const float* q_mem, int fuse_add,
                   float q_div, psgd_stream stream);
+/* psgd_p_from_m with psgd_pack_vec (or psgd_pack_vec_fused when fuse_add != 0) folded into the same launch:
+ * one kernel and one launch gap less per step.  Falls back to two launches when the streamed kernel is not in use. */
+int psgd_p_from_m_pack(psgd_plan* plan, float* p_mem, const float* q_mem, int fuse_add, float q_div,
+                       float* flat, psgd_stream stream);
 /* K2: p_mem /= n_workers then modified Gram-Schmidt of every P_i in place
  * (reducer.py:128, 136-137, 180-191). */
 int psgd_orthogonalize(psgd_plan* plan, float* p_mem, float n_workers, psgd_stream stream);
@@ -109,7 +113,11 @@ int psgd_q_from_mt(psgd_plan* plan, const float* p_mem, float* q_mem, void* work
  * q_mem itself is left untouched (still the SUM); psgd_finish scales it. */
 int psgd_finalize(psgd_plan* plan, const float* p_mem, const float* q_mem, float n_workers,
                   psgd_stream stream);
-/* K6b: vec_out_j = flat_j / n_workers (reducer.py:167-168, tensor_buffer.py:34-36) and, if
+/* psgd_finalize with the scatter half of psgd_finish (vec_out_j = flat_j / n_workers) folded into the same launch.
+ * q_mem /= n_workers still needs psgd_finish(plan, NULL-able flat, q_mem, ...) afterwards when n_workers > 1. */
+int psgd_finalize_unpack(psgd_plan* plan, const float* p_mem, const float* q_mem, float n_workers,
+                         const float* flat, psgd_stream stream);
+/* K6b: if flat != NULL, vec_out_j = flat_j / n_workers (reducer.py:167-168, tensor_buffer.py:34-36); if
  * q_mem != NULL, q_mem /= n_workers in place (reducer.py:147). */
 int psgd_finish(psgd_plan* plan, const float* flat, float* q_mem, float n_workers,
                 psgd_stream stream);

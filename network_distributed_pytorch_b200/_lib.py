@@ -34,6 +34,8 @@ SIGNATURES = {
     "psgd_pack_vec": (ctypes.c_int, [vp, vp, vp]),
     "psgd_pack_vec_fused": (ctypes.c_int, [vp, vp, vp]),
     "psgd_p_from_m": (ctypes.c_int, [vp, vp, vp, ctypes.c_int, ctypes.c_float, vp]),
+    "psgd_p_from_m_pack": (ctypes.c_int, [vp, vp, vp, ctypes.c_int, ctypes.c_float, vp, vp]),
+    "psgd_finalize_unpack": (ctypes.c_int, [vp, vp, vp, ctypes.c_float, vp, vp]),
     "psgd_orthogonalize": (ctypes.c_int, [vp, vp, ctypes.c_float, vp]),
     "psgd_q_from_mt": (ctypes.c_int, [vp, vp, vp, vp, vp]),
     "psgd_finalize": (ctypes.c_int, [vp, vp, vp, ctypes.c_float, vp]),

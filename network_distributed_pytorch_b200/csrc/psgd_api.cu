@@ -82,6 +82,8 @@ struct psgd_plan {
   StreamTask* d_tasks1 = nullptr;
   StreamTask* d_tasks4 = nullptr;
   int* d_counters = nullptr;  // [0..1] K1 task / done counters, [2..3] K4
+  int n_ctr3 = 0;
+  int* d_ctr3 = nullptr;  // K3: completion counter per (matrix, column tile), zero between launches
   unsigned long long* d_dbg = nullptr;  // PSGD_STREAM_DEBUG: per-CTA cycle breakdown of the last streamed K1
   int4* d_tiles1_fb = nullptr;
   int4* d_tiles4_fb = nullptr;
@@ -314,6 +316,7 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
 
   p->mats.resize(n_mat);
   long long po = 0, qo = 0, wo = 0;
+  int n_ctr3 = 0;
   int mmax = 0;
   size_t smem3 = 0;
   for (int i = 0; i < n_mat; ++i) {
@@ -358,7 +361,7 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
     const size_t s3 = ((size_t)md.t3_rows * R + (size_t)RL * md.cpt * R * (cgw + 1)) * 4;
     smem3 = std::max(smem3, s3);
     const int ncol = (int)((groups + cgw - 1) / cgw);
-    if (md.n && md.m)
+    if (md.n && md.m) {
       for (int b = 0; b < md.nblk3; ++b)
         for (int ct = 0; ct < ncol; ++ct) {
           ColTile t{};
@@ -367,24 +370,13 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
           t.nrows = std::min(md.t3_rows, md.n - t.row0);
           t.col0 = ct * cgw * md.cpt;
           t.blk = b;
+          t.pad0 = n_ctr3 + ct;  // completion counter of this (matrix, column tile)
           p->tiles3.push_back(t);
         }
+      n_ctr3 += ncol;
+    }
   }
-  if (env_ll("PSGD_K3_REVERSE", 1) != 0) {
-    // K1 walks the matrices in index order with the largest one last; K3 walks the same bytes backwards so
-    // that what K1 read last (still in the 126 MB L2) is what K3 reads first, and K4 (K1's order again) starts
-    // on what K3 read last.  M is read three times per step; this turns part of passes two and three into L2 hits.
-    int big = -1;
-    for (int i = 0; i < n_mat; ++i)
-      if (p->mats[i].n && p->mats[i].m &&
-          (big < 0 || (long long)p->mats[i].n * p->mats[i].m > (long long)p->mats[big].n * p->mats[big].m)) big = i;
-    std::vector<ColTile> ordered;
-    ordered.reserve(p->tiles3.size());
-    for (const ColTile& t : p->tiles3) if (t.mat != big) ordered.push_back(t);
-    for (const ColTile& t : p->tiles3) if (t.mat == big) ordered.push_back(t);
-    std::reverse(ordered.begin(), ordered.end());
-    p->tiles3.swap(ordered);
-  }
+  p->n_ctr3 = n_ctr3;
   p->p_total = po;
   p->q_total = qo;
   p->ws_total = wo;
@@ -485,6 +477,10 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
     rc |= upload(&p->d_tasks4, p->tasks4);
     if (!rc && cudaMalloc((void**)&p->d_counters, 4 * sizeof(int)) != cudaSuccess) rc = fail("cudaMalloc(counters) failed");
     if (!rc && cudaMemset(p->d_counters, 0, 4 * sizeof(int)) != cudaSuccess) rc = fail("cudaMemset(counters) failed");
+    if (!rc && p->n_ctr3) {
+      if (cudaMalloc((void**)&p->d_ctr3, (size_t)p->n_ctr3 * sizeof(int)) != cudaSuccess ||
+          cudaMemset(p->d_ctr3, 0, (size_t)p->n_ctr3 * sizeof(int)) != cudaSuccess) rc = fail("cudaMalloc(ctr3) failed");
+    }
     if (!rc && env_ll("PSGD_STREAM_DEBUG", 0)) {
       const size_t nb = (size_t)p->stream_grid * kDbgWords * sizeof(unsigned long long);
       if (cudaMalloc((void**)&p->d_dbg, nb) != cudaSuccess || cudaMemset(p->d_dbg, 0, nb) != cudaSuccess) rc = fail("cudaMalloc(dbg) failed");
@@ -528,6 +524,7 @@ int psgd_plan_destroy(psgd_plan* p) {
     cudaFree(p->d_tasks4);
     cudaFree(p->d_counters);
     cudaFree(p->d_dbg);
+    cudaFree(p->d_ctr3);
     cudaFree(p->d_tiles1_fb);
     cudaFree(p->d_tiles4_fb);
     cudaFree(p->d_orth_small);
@@ -735,8 +732,28 @@ int psgd_pack_vec(psgd_plan* p, float* flat, psgd_stream stream) {
     default: return fail("unsupported compile-time rank %d", R_); \
   }
 
+static int p_from_m_impl(psgd_plan* p, float* p_mem, const float* q_mem, int fuse_add, float q_div, float* flat,
+                         psgd_stream stream);
+
 int psgd_p_from_m(psgd_plan* p, float* p_mem, const float* q_mem, int fuse_add, float q_div, psgd_stream stream) {
+  return p_from_m_impl(p, p_mem, q_mem, fuse_add, q_div, nullptr, stream);
+}
+
+int psgd_p_from_m_pack(psgd_plan* p, float* p_mem, const float* q_mem, int fuse_add, float q_div, float* flat,
+                       psgd_stream stream) {
   if (need_device(p) || need_ptrs(p)) return 1;
+  if (p->v_total && !flat) return fail("psgd_p_from_m_pack: flat is null");
+  if (fuse_add && !p->have_vge) return fail("psgd_p_from_m_pack: fuse_add needs psgd_set_ptrs_fused");
+  return p_from_m_impl(p, p_mem, q_mem, fuse_add, q_div, flat, stream);
+}
+
+static int p_from_m_impl(psgd_plan* p, float* p_mem, const float* q_mem, int fuse_add, float q_div, float* flat,
+                         psgd_stream stream) {
+  if (need_device(p) || need_ptrs(p)) return 1;
+  const bool fold = flat && p->v_total && !p->tiles1.empty() && (fuse_add ? p->stream1f_now : p->stream1_now);
+  if (flat && p->v_total && !fold) {  // no streamed launch to ride on: separate gather
+    if (fuse_add ? psgd_pack_vec_fused(p, flat, stream) : psgd_pack_vec(p, flat, stream)) return 1;
+  }
   if (p->tiles1.empty()) return 0;
   if (!p_mem || !q_mem) return fail("psgd_p_from_m: null p_mem/q_mem");
   if (fuse_add && !p->have_ge) return fail("psgd_p_from_m: fuse_add needs grad/err pointers in psgd_set_ptrs");
@@ -747,7 +764,8 @@ int psgd_p_from_m(psgd_plan* p, float* p_mem, const float* q_mem, int fuse_add, 
   const unsigned grid = (unsigned)p->tiles1.size();
   PhaseScope ts(p, PSGD_PHASE_P_FROM_M, s);
   if (fuse_add ? p->stream1f_now : p->stream1_now) {
-    StreamPlan sp{p->d_tasks1, p->d_counters, (int)p->tasks1.size(), p->ring_slot_bytes, p->ring_slots, p->q_bytes, p->d_dbg};
+    StreamPlan sp{p->d_tasks1, p->d_counters, (int)p->tasks1.size(), p->ring_slot_bytes, p->ring_slots, p->q_bytes, p->d_dbg,
+                  p->d_vtiles, flat, fold ? (int)p->vtiles.size() : 0, fold ? (fuse_add ? 2 : 1) : 0, 1.0f};
     DISPATCH_R(p->R, {
       if (fuse_add) {
         if (!p->attr1f_set) CU(cudaFuncSetAttribute((const void*)k_p_from_m_stream<RR, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->stream_smem));
@@ -847,16 +865,17 @@ int psgd_q_from_mt(psgd_plan* p, const float* p_mem, float* q_mem, void* workspa
   cudaStream_t s = (cudaStream_t)stream;
   const DevPlan dp = dev_plan(p);
   float* ws = (float*)workspace;
+  const bool fold = p->d_ctr3 && env_ll("PSGD_K3_FOLD", 1) != 0;
   {
     PhaseScope ts(p, PSGD_PHASE_Q_FROM_MT, s);
     const unsigned grid = (unsigned)p->tiles3.size();
     DISPATCH_R(p->R, {
       if (set_smem(k_q_from_mt<RR>, p->smem3)) return 1;
-      k_q_from_mt<RR><<<grid, kThreads, p->smem3, s>>>(dp, p->slot, p_mem, ws);
+      k_q_from_mt<RR><<<grid, kThreads, p->smem3, s>>>(dp, p->slot, p_mem, ws, q_mem, fold ? p->d_ctr3 : nullptr);
     });
     if (check_launch("k_q_from_mt")) return 1;
   }
-  {
+  if (!fold) {
     PhaseScope ts(p, PSGD_PHASE_Q_REDUCE, s);
     k_q_reduce<<<(unsigned)p->qtiles.size(), kThreads, 0, s>>>(dp, ws, q_mem);
     if (check_launch("k_q_reduce")) return 1;
@@ -864,8 +883,27 @@ int psgd_q_from_mt(psgd_plan* p, const float* p_mem, float* q_mem, void* workspa
   return 0;
 }
 
+static int finalize_impl(psgd_plan* p, const float* p_mem, const float* q_mem, float n_workers, const float* flat,
+                         psgd_stream stream);
+
 int psgd_finalize(psgd_plan* p, const float* p_mem, const float* q_mem, float n_workers, psgd_stream stream) {
+  return finalize_impl(p, p_mem, q_mem, n_workers, nullptr, stream);
+}
+
+int psgd_finalize_unpack(psgd_plan* p, const float* p_mem, const float* q_mem, float n_workers, const float* flat,
+                         psgd_stream stream) {
   if (need_device(p) || need_ptrs(p)) return 1;
+  if (p->v_total && !flat) return fail("psgd_finalize_unpack: flat is null");
+  return finalize_impl(p, p_mem, q_mem, n_workers, flat, stream);
+}
+
+static int finalize_impl(psgd_plan* p, const float* p_mem, const float* q_mem, float n_workers, const float* flat,
+                         psgd_stream stream) {
+  if (need_device(p) || need_ptrs(p)) return 1;
+  const bool fold = flat && p->v_total && !p->tiles4.empty() && p->stream4_now;
+  if (flat && p->v_total && !fold) {  // no streamed launch to ride on: separate scatter
+    if (psgd_finish(p, flat, nullptr, n_workers, stream)) return 1;
+  }
   if (p->tiles4.empty()) return 0;
   if (!p_mem || !q_mem) return fail("psgd_finalize: null p_mem/q_mem");
   if (!(n_workers >= 1.f)) return fail("psgd_finalize: n_workers must be >= 1");
@@ -875,7 +913,8 @@ int psgd_finalize(psgd_plan* p, const float* p_mem, const float* q_mem, float n_
   const unsigned grid = (unsigned)p->tiles4.size();
   PhaseScope ts(p, PSGD_PHASE_FINALIZE, s);
   if (p->stream4_now) {
-    StreamPlan sp{p->d_tasks4, p->d_counters + 2, (int)p->tasks4.size(), p->ring_slot_bytes, p->ring_slots, p->q_bytes, nullptr};
+    StreamPlan sp{p->d_tasks4, p->d_counters + 2, (int)p->tasks4.size(), p->ring_slot_bytes, p->ring_slots, p->q_bytes, nullptr,
+                  p->d_vtiles, const_cast<float*>(flat), fold ? (int)p->vtiles.size() : 0, fold ? 3 : 0, n_workers};
     DISPATCH_R(p->R, {
       if (!p->attr4_set) CU(cudaFuncSetAttribute((const void*)k_finalize_stream<RR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->stream_smem));
       p->attr4_set = true;
@@ -904,14 +943,13 @@ int psgd_finish(psgd_plan* p, const float* flat, float* q_mem, float n_workers, 
   if (need_device(p) || need_ptrs(p)) return 1;
   if (!(n_workers >= 1.f)) return fail("psgd_finish: n_workers must be >= 1");
   const long long qn = q_mem ? p->q_total : 0;
-  const long long total = p->v_total + qn;
-  if (total == 0) return 0;
-  if (p->v_total && !flat) return fail("psgd_finish: flat is null");
+  const size_t nvt = flat ? p->vtiles.size() : 0;  // flat == NULL: the scatter was folded into psgd_finalize_unpack
+  if (nvt == 0 && qn == 0) return 0;
   CU(cudaSetDevice(p->device));
   cudaStream_t s = (cudaStream_t)stream;
   PhaseScope ts(p, PSGD_PHASE_FINISH, s);
-  const unsigned grid = (unsigned)(p->vtiles.size() + (size_t)((qn + kVecTileElems - 1) / kVecTileElems));
-  k_finish<<<grid, kThreads, 0, s>>>(dev_plan(p), p->slot, flat, (int)p->vtiles.size(), q_mem, qn, n_workers);
+  const unsigned grid = (unsigned)(nvt + (size_t)((qn + kVecTileElems - 1) / kVecTileElems));
+  k_finish<<<grid, kThreads, 0, s>>>(dev_plan(p), p->slot, flat, (int)nvt, q_mem, qn, n_workers);
   return check_launch("k_finish");
 }
 

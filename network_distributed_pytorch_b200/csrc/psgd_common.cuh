@@ -217,14 +217,4 @@ __device__ __forceinline__ float warp_sum(float x) {
   return x;
 }
 
-// index of the last prefix entry <= x  (pre has n + 1 entries, pre[0] = 0)
-__device__ __forceinline__ int find_segment(const long long* __restrict__ pre, int n, long long x) {
-  int lo = 0, hi = n;  // answer in [lo, hi)
-  while (hi - lo > 1) {
-    const int mid = (lo + hi) >> 1;
-    if (__ldg(pre + mid) <= x) lo = mid; else hi = mid;
-  }
-  return lo;
-}
-
 }  // namespace psgd

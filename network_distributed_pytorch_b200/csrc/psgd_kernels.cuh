@@ -533,9 +533,14 @@ __device__ __forceinline__ void q_tile(const MatDesc& md, const ColTile& t, cons
   }
 }
 
+// `done` (optional): one counter per (matrix, column tile).  The CTA that completes the last row block of a
+// column tile sums that tile's partials over the row blocks, in block order, straight into q_mem -- the second
+// stage without a second launch.  Which CTA does the summing varies from run to run, the order of the sum does
+// not, so the result stays deterministic.  The counter is left at zero for the next launch.
 template <int R>
 __global__ void __launch_bounds__(kThreads, 2)
-k_q_from_mt(DevPlan pl, PtrSlot ps, const float* __restrict__ p_mem, float* __restrict__ ws) {
+k_q_from_mt(DevPlan pl, PtrSlot ps, const float* __restrict__ p_mem, float* __restrict__ ws, float* __restrict__ q_mem,
+            int* __restrict__ done) {
   extern __shared__ __align__(16) float smem[];
   const ColTile t = pl.tiles3[blockIdx.x];
   const MatDesc md = pl.mats[t.mat];
@@ -549,6 +554,51 @@ k_q_from_mt(DevPlan pl, PtrSlot ps, const float* __restrict__ p_mem, float* __re
   } else {
     q_tile<R, 1, false>(md, t, M, P, ws, smem);
   }
+  if (done == nullptr) return;
+
+  __shared__ int s_last;
+  __threadfence();  // this CTA's partial is visible device-wide before it is counted
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = (atomicAdd(&done[t.pad0], 1) == md.nblk3 - 1);
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  const int r = md.r, m = md.m;
+  const int wcols = min(md.cgw * md.cpt, m - t.col0);
+  const size_t stride = (size_t)m * r;
+  const size_t e0 = (size_t)t.col0 * r;
+  const int count = wcols * r;
+  const float* src = ws + md.ws_off + e0;
+  float* dst = q_mem + md.q_off + e0;
+  const int nb = md.nblk3;
+  if ((stride & 3) == 0 && (count & 3) == 0) {
+    for (int f = threadIdx.x; f < (count >> 2); f += kThreads) {
+      float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
+      int b = 0;
+      for (; b + 4 <= nb; b += 4) {
+        const float4 v0 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)b * stride) + f);
+        const float4 v1 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(b + 1) * stride) + f);
+        const float4 v2 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(b + 2) * stride) + f);
+        const float4 v3 = __ldcg(reinterpret_cast<const float4*>(src + (size_t)(b + 3) * stride) + f);
+        sum.x = (((sum.x + v0.x) + v1.x) + v2.x) + v3.x;
+        sum.y = (((sum.y + v0.y) + v1.y) + v2.y) + v3.y;
+        sum.z = (((sum.z + v0.z) + v1.z) + v2.z) + v3.z;
+        sum.w = (((sum.w + v0.w) + v1.w) + v2.w) + v3.w;
+      }
+      for (; b < nb; ++b) {
+        const float4 v = __ldcg(reinterpret_cast<const float4*>(src + (size_t)b * stride) + f);
+        sum.x += v.x; sum.y += v.y; sum.z += v.z; sum.w += v.w;
+      }
+      dst[4 * f] = sum.x; dst[4 * f + 1] = sum.y; dst[4 * f + 2] = sum.z; dst[4 * f + 3] = sum.w;
+    }
+  } else {
+    for (int e = threadIdx.x; e < count; e += kThreads) {
+      float sum = 0.f;
+      for (int b = 0; b < nb; ++b) sum += __ldcg(src + (size_t)b * stride + e);
+      dst[e] = sum;
+    }
+  }
+  if (threadIdx.x == 0) done[t.pad0] = 0;
 }
 
 // stage 2: q_mem[e] = sum over row blocks, in block order.  One tile = kQTileElems consecutive elements

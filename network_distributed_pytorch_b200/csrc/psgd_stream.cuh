@@ -36,7 +36,43 @@ struct StreamPlan {
   int n_slots;
   int q_bytes;           // bytes reserved for the transposed Q stage
   unsigned long long* dbg;  // optional per-CTA cycle breakdown (PSGD_STREAM_DEBUG), else nullptr
+  // side job folded into the launch (saves a kernel and its gap): the flat <=1-D buffer
+  const VecTile* vtiles;
+  float* flat;
+  int n_vtiles;
+  int vec_mode;          // 0 none, 1 pack, 2 pack with grad + err, 3 unpack (/ world)
+  float vec_world;
 };
+
+// The flat-buffer gather / scatter of the <=1-D tensors as a side job of a streamed kernel: the consumer threads
+// of CTA b take tiles b, b + gridDim.x, ... (a few KB each) while the producer's first copies are in flight.
+__device__ __forceinline__ void stream_vec_side_job(const StreamPlan& sp, const PtrSlot& ps) {
+  constexpr int NT = kConsumerWarps * 32;
+  for (int t = blockIdx.x; t < sp.n_vtiles; t += gridDim.x) {
+    const VecTile vt = sp.vtiles[t];
+    float* f = sp.flat + vt.flat_off;
+    if (sp.vec_mode == 1) {
+      const float* s = ps.vin[vt.tensor] + vt.start;
+      for (int i = threadIdx.x; i < vt.count; i += NT) f[i] = s[i];
+    } else if (sp.vec_mode == 2) {
+      const float* g = ps.vg[vt.tensor] + vt.start;
+      const float* e = ps.ve[vt.tensor] + vt.start;
+      float* send = const_cast<float*>(ps.vin[vt.tensor]) + vt.start;
+      for (int i = threadIdx.x; i < vt.count; i += NT) {
+        const float v = g[i] + e[i];
+        send[i] = v;
+        f[i] = v;
+      }
+    } else if (sp.vec_mode == 3) {
+      float* d = ps.vout[vt.tensor] + vt.start;
+      if (sp.vec_world != 1.0f) {
+        for (int i = threadIdx.x; i < vt.count; i += NT) d[i] = f[i] / sp.vec_world;
+      } else {
+        for (int i = threadIdx.x; i < vt.count; i += NT) d[i] = f[i];
+      }
+    }
+  }
+}
 constexpr int kDbgWords = 8;  // per CTA: t0, t1 (ns), cycles: desc wait, data wait, Q units, total, units, switches
 
 // what travels with a slot: an M unit {mat, row0, nrows > 0, rot}, a Q unit {mat, j0, -count, flags},
@@ -290,6 +326,7 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
     return;
   }
 
+  if (sp.vec_mode) stream_vec_side_job(sp, ps);
   int cur_mat = -1, m = 0, r = 0, pitch = 0;
   float* P = nullptr;
   float* Mw = nullptr;  // FUSE: the send buffer M is written to
@@ -415,6 +452,7 @@ k_finalize_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
     return;
   }
 
+  if (sp.vec_mode) stream_vec_side_job(sp, ps);
   int cur_mat = -1, m = 0, r = 0, pitch = 0;
   const float* P = nullptr;
   float* Out = nullptr;

@@ -90,6 +90,16 @@ class CudaPlan:
         _lib.check(self._lib.psgd_p_from_m(self._h, p_mem.data_ptr(), q_mem.data_ptr(), int(fuse_add),
                                            float(q_div), _stream(self.device)), self._lib)
 
+    def p_from_m_pack(self, p_mem, q_mem, flat, fuse_add=False, q_div=1.0):
+        """p_from_m with the flat-buffer gather folded into the same launch."""
+        _lib.check(self._lib.psgd_p_from_m_pack(self._h, p_mem.data_ptr(), q_mem.data_ptr(), int(fuse_add),
+                                                float(q_div), flat.data_ptr(), _stream(self.device)), self._lib)
+
+    def finalize_unpack(self, p_mem, q_mem, n_workers, flat):
+        """finalize with the scatter of the flat buffer folded into the same launch."""
+        _lib.check(self._lib.psgd_finalize_unpack(self._h, p_mem.data_ptr(), q_mem.data_ptr(), float(n_workers),
+                                                  flat.data_ptr(), _stream(self.device)), self._lib)
+
     def orthogonalize(self, p_mem, n_workers):
         _lib.check(self._lib.psgd_orthogonalize(self._h, p_mem.data_ptr(), float(n_workers),
                                                 _stream(self.device)), self._lib)

@@ -206,18 +206,22 @@ class PowerSGDReducer(Reducer):
         else:
             p_in, flat_in, q_in = self.p_memory, flat, self.q_memory
 
-        # [For Rank 1] pack the flat buffer now; it travels with P in one collective below
-        # (upstream starts its own async all-reduce after step 4, reducer.py:131-133; the sums are the same)
-        if fused:
-            plan.pack_vec_fused(flat_in)
-        else:
-            plan.pack_vec(flat_in)
+        # [For Rank 1] the flat buffer is gathered inside the first P = M Q launch and travels with P in one collective
+        # (upstream packs after step 4 and runs its own async all-reduce, reducer.py:131-133; the sums are the same)
+        fold = hasattr(plan, "p_from_m_pack")
+        if not fold:
+            if fused:
+                plan.pack_vec_fused(flat_in)
+            else:
+                plan.pack_vec(flat_in)
         bits_communicated += 8 * flat.nelement() * flat.element_size()
 
         for it in range(self.extra_power_iterations + 1):
             # Step 3 (reducer.py:121-123) P <- M Q
-            plan.p_from_m(p_in, self.q_memory, fuse_add=(fused and it == 0),
-                          q_div=(world if it > 0 else 1.0))
+            if fold and it == 0:
+                plan.p_from_m_pack(p_in, self.q_memory, flat_in, fuse_add=fused)
+            else:
+                plan.p_from_m(p_in, self.q_memory, fuse_add=(fused and it == 0), q_div=(world if it > 0 else 1.0))
             # Step 4 (reducer.py:126-128) ALL_REDUCE_MEAN(P); the divide is folded into step 5
             if px is not None:
                 px.allreduce(0, self._p_and_flat, n_pf)
@@ -236,10 +240,14 @@ class PowerSGDReducer(Reducer):
             bits_communicated += n_bits(self.q_memory)
 
         # Step 8 + 9 (reducer.py:158-163) decompress and memorise the local error in one sweep
-        plan.finalize(self.p_memory, self.q_memory, world)
-
-        # [For Rank 1] (reducer.py:166-168) wait, mean, scatter; q_memory becomes the mean in place
-        plan.finish(flat, self.q_memory if world > 1 else None, world)
+        # [For Rank 1] (reducer.py:166-168) mean + scatter ride on the same launch; q_memory becomes the mean in place
+        if fold:
+            plan.finalize_unpack(self.p_memory, self.q_memory, world, flat)
+            if world > 1:
+                plan.finish(None, self.q_memory, world)
+        else:
+            plan.finalize(self.p_memory, self.q_memory, world)
+            plan.finish(flat, self.q_memory if world > 1 else None, world)
         return bits_communicated
 
 
