@@ -69,11 +69,12 @@ def load():
     global _lib
     if _lib is not None:
         return _lib
-    if not os.path.exists(LIB_PATH):
+    path = os.environ.get("PSGD_LIB_PATH", LIB_PATH)  # development aid: A/B two builds in one process tree
+    if not os.path.exists(path):
         raise PsgdError(
             f"{LIB_PATH} is missing: build it with `python -m network_distributed_pytorch_b200.build` "
             "(or __graft_entry__.build()).  There is no CPU or PyTorch fallback for the reducer hot path.")
-    lib = ctypes.CDLL(LIB_PATH)
+    lib = ctypes.CDLL(path)
     for name, (res, args) in SIGNATURES.items():
         fn = getattr(lib, name)  # AttributeError here = header/library mismatch
         fn.restype = res
