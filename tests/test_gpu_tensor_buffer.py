@@ -50,3 +50,21 @@ def test_errors_and_world1_collectives():
     tbm.all_gather(out, tb.buffer)
     assert out[0].data_ptr() == tb.buffer.data_ptr()  # tensor_buffer.py:68-69 aliases
     assert dist.get_world_size() == 1
+
+
+def test_dense_reducer_world1_is_a_copy():
+    from network_distributed_pytorch_b200.dense import DenseReducer
+    from tests.gpu_common import ensure_group
+
+    ensure_group()
+    dev = torch.device("cuda", 0)
+    shapes = [(64, 33), (7,), (3, 5, 2)]
+    g = [torch.randn(s, device=dev) for s in shapes]
+    out = [torch.zeros(s, device=dev) for s in shapes]
+    red = DenseReducer(714, dev)
+    bits = red.reduce(g, out, None)
+    assert bits == 32 * sum(t.nelement() for t in g)
+    assert all(torch.equal(a, b) for a, b in zip(g, out))
+    g2 = [t * 2 for t in g]
+    red.reduce(g2, out, None)
+    assert all(torch.equal(a, b) for a, b in zip(g2, out))
