@@ -1,95 +1,113 @@
-"""Host mirror of the upstream ``tensor_buffer.py`` (ddp_powersgd_guide_cifar10/tensor_buffer.py):
-same class, methods and module functions; the flatten / unflatten copies are a single
-gather / scatter kernel over a device pointer table instead of ``torch.cat`` and a Python loop of
-``tensor[:] = entry`` (tensor_buffer.py:19, :27-36).  The flat layout is bit-identical to
-``torch.cat([t.view(-1) for t in tensors])``: running offsets, no padding, dtype of the inputs.
+"""Flat-buffer packer with the interface of the upstream ``tensor_buffer.py``
+(ddp_powersgd_guide_cifar10/tensor_buffer.py:4-69): ``TensorBuffer(tensors)`` with ``buffer``, indexing, ``len``,
+``pack``, ``unpack``, ``nelement``, ``element_size``, ``bits``, ``all_reduce``, ``all_gather`` and the two guarded
+module-level collectives.  The semantics are upstream's -- the flat layout is bit-identical to
+``torch.cat([t.view(-1) for t in tensors])`` (running offsets, no padding, dtype of the inputs) -- the mechanics are
+not: flattening and un-flattening are ONE gather / scatter kernel over a device pointer table
+(``psgd_tb_pack`` / ``psgd_tb_unpack``) instead of ``torch.cat`` plus a Python loop of per-tensor copies.
+CUDA tensors only; there is no CPU fallback.
 """
 import ctypes
+from itertools import accumulate
 
 import torch
+import torch.distributed as dist
 
 
-class TensorBuffer():
-    """
-    Packs multiple tensors into one flat buffer for efficient
-    intra-worker communication.
-    """
+def _world_size():
+    return dist.get_world_size() if dist.is_available() else 1
+
+
+class TensorBuffer:
+    """One contiguous buffer holding the elements of a list of tensors, in list order."""
 
     def __init__(self, tensors):
-        tensors = list(tensors)
-        if len(tensors) == 0:
-            # upstream: torch.cat([]) (tensor_buffer.py:19)
+        members = list(tensors)
+        if not members:
+            # what torch.cat([]) says upstream (tensor_buffer.py:19)
             raise RuntimeError("torch.cat(): expected a non-empty list of Tensors")
-        indices = [0]
-        for tensor in tensors:
-            indices.append(indices[-1] + tensor.nelement())
-        self._start_idx = indices[:-1]
-        self._end_idx = indices[1:]
-        self._tensors = tensors
-
-        first = tensors[0]
-        if first.device.type != "cuda":
+        head = members[0]
+        if head.device.type != "cuda":
             raise RuntimeError("TensorBuffer (B200 build) packs CUDA tensors only; there is no CPU fallback")
-        for t in tensors:
-            if t.dtype != first.dtype or t.device != first.device:
-                raise RuntimeError("TensorBuffer: all tensors must share dtype and device (torch.cat would raise too)")
+        if any(t.dtype != head.dtype or t.device != head.device for t in members):
+            raise RuntimeError("TensorBuffer: all tensors must share dtype and device (torch.cat would raise too)")
+
+        counts = [t.nelement() for t in members]
+        self._bounds = [0, *accumulate(counts)]  # prefix sums: entry i starts at _bounds[i], ends at _bounds[i + 1]
+        self._tensors = members
+        self._device = head.device
+
         from . import _lib
 
         self._libmod = _lib
         self._lib = _lib.load()
-        self._device = first.device
         handle = ctypes.c_void_p()
-        _lib.check(self._lib.psgd_tb_create(len(tensors), _lib.i64_array([t.nelement() for t in tensors]),
-                                            first.element_size(), first.device.index, ctypes.byref(handle)),
-                   self._lib)
+        _lib.check(self._lib.psgd_tb_create(len(members), _lib.i64_array(counts), head.element_size(),
+                                            head.device.index, ctypes.byref(handle)), self._lib)
         self._h = handle
-        self.buffer = torch.empty(indices[-1], dtype=first.dtype, device=first.device)
-        self.pack()  # copies
+        self.buffer = torch.empty(self._bounds[-1], dtype=head.dtype, device=head.device)
+        self.pack()
 
     def __del__(self):
-        h, self._h = getattr(self, "_h", None), None
-        if h:
+        handle, self._h = getattr(self, "_h", None), None
+        if handle:
             try:
-                self._lib.psgd_tb_destroy(h)
+                self._lib.psgd_tb_destroy(handle)
             except Exception:
                 pass
 
-    def _stream(self):
-        return ctypes.c_void_p(torch.cuda.current_stream(self._device).cuda_stream)
+    # upstream exposes these two lists; keep them readable
+    @property
+    def _start_idx(self):
+        return self._bounds[:-1]
 
-    def _same_layout(self, tensors):
-        if len(tensors) != len(self._tensors):
-            return False
-        return all(t.is_contiguous() and t.dtype == self.buffer.dtype and t.device == self.buffer.device
-                   and t.nelement() == e - s for t, s, e in zip(tensors, self._start_idx, self._end_idx))
-
-    def __getitem__(self, index):
-        return self.buffer[self._start_idx[index] : self._end_idx[index]].view(*self._tensors[index].shape)
+    @property
+    def _end_idx(self):
+        return self._bounds[1:]
 
     def __len__(self):
         return len(self._tensors)
 
+    def __getitem__(self, index):
+        lo, hi = self._bounds[index], self._bounds[index + 1]
+        return self.buffer.narrow(0, lo, hi - lo).view(self._tensors[index].shape)
+
+    # ------------------------------------------------------------------------------------------------
+    def _kernel_ok(self, tensors):
+        """True when the list can go through the pointer-table kernel: same count, sizes, dtype, device, packed."""
+        if len(tensors) != len(self._tensors):
+            return False
+        spans = zip(tensors, self._bounds, self._bounds[1:])
+        return all(t.is_contiguous() and t.dtype == self.buffer.dtype and t.device == self.buffer.device
+                   and t.nelement() == hi - lo for t, lo, hi in spans)
+
+    def _launch(self, entry, tensors, *, into_buffer):
+        ptrs = self._libmod.ptr_array([t.data_ptr() for t in tensors])
+        stream = ctypes.c_void_p(torch.cuda.current_stream(self._device).cuda_stream)
+        flat = self.buffer.data_ptr()
+        rc = entry(self._h, ptrs, flat, stream) if into_buffer else entry(self._h, flat, ptrs, stream)
+        self._libmod.check(rc, self._lib)
+
     def pack(self, tensors=None):
-        # Optional. init already does this.
-        if tensors is None:
-            tensors = self._tensors
-        tensors = list(tensors)
-        if self._same_layout(tensors):
-            ptrs = self._libmod.ptr_array([t.data_ptr() for t in tensors])
-            self._libmod.check(self._lib.psgd_tb_pack(self._h, ptrs, self.buffer.data_ptr(), self._stream()), self._lib)
-        else:  # broadcasting / strided / converting assignments keep upstream's per-entry semantics
-            for tensor, entry in zip(tensors, self):
-                entry[:] = tensor
+        """buffer <- tensors (the constructor has already done this for the original list)."""
+        source = self._tensors if tensors is None else list(tensors)
+        if self._kernel_ok(source):
+            self._launch(self._lib.psgd_tb_pack, source, into_buffer=True)
+            return
+        # broadcasting, strided or converting assignments: upstream's per-entry semantics
+        for i, t in enumerate(source[: len(self)]):
+            self[i][...] = t
 
     def unpack(self, tensors):
-        tensors = list(tensors)
-        if self._same_layout(tensors):
-            ptrs = self._libmod.ptr_array([t.data_ptr() for t in tensors])
-            self._libmod.check(self._lib.psgd_tb_unpack(self._h, self.buffer.data_ptr(), ptrs, self._stream()), self._lib)
-        else:
-            for tensor, entry in zip(tensors, self):
-                tensor[:] = entry
+        """tensors <- buffer."""
+        targets = list(tensors)
+        if self._kernel_ok(targets):
+            self._launch(self._lib.psgd_tb_unpack, targets, into_buffer=False)
+            return
+        for i, t in enumerate(targets[: len(self)]):
+            t[...] = self[i]
 
+    # ------------------------------------------------------------------------------------------------
     def nelement(self):
         return self.buffer.nelement()
 
@@ -97,29 +115,29 @@ class TensorBuffer():
         return self.buffer.element_size()
 
     def bits(self):
-        return 8 * self.nelement() * self.element_size()
+        return self.buffer.nelement() * self.buffer.element_size() * 8
 
     def all_reduce(self, async_op=False):
-        return torch.distributed.all_reduce(self.buffer, async_op=async_op)
+        # unguarded on purpose, like upstream: needs an initialised process group even for one worker
+        return dist.all_reduce(self.buffer, async_op=async_op)
 
     def all_gather(self, async_op=False):
-        n_workers = torch.distributed.get_world_size() if torch.distributed.is_available() else 1
-        buffers = [torch.empty_like(self.buffer) for i in range(n_workers)]
-        handle = all_gather(buffers, self.buffer, async_op=async_op)
-        if async_op:
-            return buffers, handle
-        else:
-            return buffers
+        copies = [torch.empty_like(self.buffer) for _ in range(_world_size())]
+        work = all_gather(copies, self.buffer, async_op=async_op)
+        return (copies, work) if async_op else copies
 
 
 def all_reduce(*args, **kwargs):
-    if torch.distributed.is_available() and torch.distributed.get_world_size() > 1:
-        return torch.distributed.all_reduce(*args, **kwargs)
+    """dist.all_reduce, skipped (returns None) when there is a single worker."""
+    if dist.is_available() and dist.get_world_size() > 1:
+        return dist.all_reduce(*args, **kwargs)
+    return None
 
 
 def all_gather(out_list, in_tensor, **kwargs):
-    if torch.distributed.is_available() and torch.distributed.get_world_size() > 1:
-        return torch.distributed.all_gather(out_list, in_tensor, **kwargs)
-    else:
-        assert len(out_list) == 1
-        out_list[0].data = in_tensor
+    """dist.all_gather; with a single worker the only output simply aliases the input."""
+    if dist.is_available() and dist.get_world_size() > 1:
+        return dist.all_gather(out_list, in_tensor, **kwargs)
+    assert len(out_list) == 1
+    out_list[0].data = in_tensor
+    return None
