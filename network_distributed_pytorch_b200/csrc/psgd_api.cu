@@ -71,6 +71,8 @@ struct psgd_plan {
   int wc_cap = 0;
   int n_max = 0;
   std::vector<int> orth_small, orth_tall, orth_generic;  // K2 routing by row count
+  int orth_tall_cluster = kOrthCluster;
+  bool orth16_attr = false;
   int *d_orth_small = nullptr, *d_orth_tall = nullptr, *d_orth_generic = nullptr;
   size_t smem1 = 0, smem3 = 0, smem4 = 0;
   // streamed (bulk-copy ring) path for K1 / K4
@@ -432,11 +434,12 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
 
   {  // K2 routing: register-resident single CTA, register-resident cluster, or generic cluster
     const int rpt = R <= 8 ? 4 : 2;
+    p->orth_tall_cluster = (R == 16) ? kOrthClusterMax : kOrthCluster;  // R = 16 keeps only 2 rows per thread
     for (int i = 0; i < n_mat; ++i) {
       const long long nn = p->mats[i].n;
       if (nn == 0 || p->mats[i].m == 0) continue;
       if (R <= 16 && nn <= (long long)kOrthSmallThreads * rpt) p->orth_small.push_back(i);
-      else if (R <= 16 && nn <= (long long)kOrthCluster * kOrthSmallThreads * rpt) p->orth_tall.push_back(i);
+      else if (R <= 16 && nn <= (long long)p->orth_tall_cluster * kOrthSmallThreads * rpt) p->orth_tall.push_back(i);
       else p->orth_generic.push_back(i);
     }
   }
@@ -560,7 +563,7 @@ int psgd_tile_count(const psgd_plan* p, int phase) {
     case PSGD_PHASE_P_FROM_M: return (int)p->tiles1.size();
     case PSGD_PHASE_FINALIZE: return (int)p->tiles4.size();
     case PSGD_PHASE_Q_FROM_MT: return (int)p->tiles3.size();
-    case PSGD_PHASE_ORTH: return (int)(p->orth_small.size() + (p->orth_tall.size() + p->orth_generic.size()) * kOrthCluster);
+    case PSGD_PHASE_ORTH: return (int)(p->orth_small.size() + p->orth_tall.size() * p->orth_tall_cluster + p->orth_generic.size() * kOrthCluster);
     default: return 0;
   }
 }
@@ -831,13 +834,14 @@ int psgd_orthogonalize(psgd_plan* p, float* p_mem, float n_workers, psgd_stream 
     const int* d_ids = pass == 0 ? p->d_orth_tall : p->d_orth_generic;
     if (ids.empty()) continue;
     cudaLaunchConfig_t cfg{};
-    cfg.gridDim = dim3((unsigned)ids.size() * kOrthCluster);
+    const int csz = pass == 0 ? p->orth_tall_cluster : kOrthCluster;
+    cfg.gridDim = dim3((unsigned)ids.size() * csz);
     cfg.blockDim = dim3(pass == 0 ? kOrthSmallThreads : kOrthThreads);
     cfg.dynamicSmemBytes = 0;
     cfg.stream = s;
     cudaLaunchAttribute at[1];
     at[0].id = cudaLaunchAttributeClusterDimension;
-    at[0].val.clusterDim.x = kOrthCluster;
+    at[0].val.clusterDim.x = csz;
     at[0].val.clusterDim.y = 1;
     at[0].val.clusterDim.z = 1;
     cfg.attrs = at;
@@ -846,6 +850,8 @@ int psgd_orthogonalize(psgd_plan* p, float* p_mem, float n_workers, psgd_stream 
       if (p->R <= 8) {
         DISPATCH_R8(p->R, { CU(cudaLaunchKernelEx(&cfg, k_orth_tall<RR, 4>, dp, d_ids, p_mem, n_workers)); });
       } else {
+        if (!p->orth16_attr) CU(cudaFuncSetAttribute((const void*)k_orth_tall<16, 2>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        p->orth16_attr = true;
         CU(cudaLaunchKernelEx(&cfg, k_orth_tall<16, 2>, dp, d_ids, p_mem, n_workers));
       }
     } else {

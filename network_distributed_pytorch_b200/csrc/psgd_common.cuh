@@ -10,6 +10,7 @@ constexpr int kWarps = kThreads / 32;
 constexpr int kOrthThreads = 512;  // CTA size of the generic (global-memory) Gram-Schmidt kernel
 constexpr int kOrthSmallThreads = 1024;  // CTA size of the register-resident Gram-Schmidt kernels
 constexpr int kOrthCluster = 8;    // CTAs per matrix (one thread-block cluster)
+constexpr int kOrthClusterMax = 16;  // non-portable cluster size used for tall matrices at R = 16
 
 // per-matrix constants, uploaded once per plan
 struct MatDesc {

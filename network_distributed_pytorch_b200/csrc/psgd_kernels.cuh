@@ -274,7 +274,7 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
                                             int crank, int csize) {
   constexpr int LPV = 32 / R;  // lanes per value after a warp_fold<R>
   __shared__ __align__(16) float wsum[32][R];
-  __shared__ __align__(16) float part[2][kOrthCluster][R];
+  __shared__ __align__(16) float part[2][kOrthClusterMax][R];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nthr = blockDim.x, nwarp = nthr >> 5;
   const int per = (n + csize - 1) / csize;
@@ -335,7 +335,7 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
           if (csize > 1) {
             for (int dst = 0; dst < csize; ++dst) {
               float* remote = cg::this_cluster().map_shared_rank(&part[0][0][0], dst);
-              remote[(par * kOrthCluster + crank) * R + j] = w;
+              remote[(par * kOrthClusterMax + crank) * R + j] = w;
             }
           } else {
             part[par][0][j] = w;
