@@ -81,6 +81,10 @@ struct psgd_plan {
   std::vector<char> eligible;
   std::vector<StreamTask> tasks1, tasks4;
   std::vector<int4> tiles1_fb, tiles4_fb;  // direct-load tiles of the matrices that do not qualify
+  std::vector<int> direct_ids;             // ... except the tiny ones, done as a side job of the streamed launch
+  int* d_direct_ids = nullptr;
+  std::vector<int> direct_row_pre;
+  int* d_direct_row_pre = nullptr;
   StreamTask* d_tasks1 = nullptr;
   StreamTask* d_tasks4 = nullptr;
   int* d_counters = nullptr;  // [0..1] K1 task / done counters, [2..3] K4
@@ -425,8 +429,20 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
       p->stream_smem = (size_t)qb + (size_t)slots * slot + kStreamSmemExtra;
       build_stream_tasks(p, rows1, p->tasks1);
       build_stream_tasks(p, rows4, p->tasks4);
-      for (const int4& t : p->tiles1) if (!p->eligible[t.x]) p->tiles1_fb.push_back(t);
-      for (const int4& t : p->tiles4) if (!p->eligible[t.x]) p->tiles4_fb.push_back(t);
+      // tiny matrices that do not qualify ride on the streamed launch as a side job; the rest get their own launch
+      std::vector<char> side(n_mat, 0);
+      const long long side_max = env_ll("PSGD_SIDE_MAX_ELEMS", 64 * 1024);
+      for (int i = 0; i < n_mat; ++i) {
+        const MatDesc& md = p->mats[i];
+        if (!p->eligible[i] && md.n && md.m && (long long)md.n * md.m <= side_max) {
+          side[i] = 1;
+          if (p->direct_row_pre.empty()) p->direct_row_pre.push_back(0);
+          p->direct_ids.push_back(i);
+          p->direct_row_pre.push_back(p->direct_row_pre.back() + md.n);
+        }
+      }
+      for (const int4& t : p->tiles1) if (!p->eligible[t.x] && !side[t.x]) p->tiles1_fb.push_back(t);
+      for (const int4& t : p->tiles4) if (!p->eligible[t.x] && !side[t.x]) p->tiles4_fb.push_back(t);
     } else {
       p->eligible.assign(n_mat, 0);
     }
@@ -488,6 +504,8 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
       const size_t nb = (size_t)p->stream_grid * kDbgWords * sizeof(unsigned long long);
       if (cudaMalloc((void**)&p->d_dbg, nb) != cudaSuccess || cudaMemset(p->d_dbg, 0, nb) != cudaSuccess) rc = fail("cudaMalloc(dbg) failed");
     }
+    rc |= upload(&p->d_direct_ids, p->direct_ids);
+    rc |= upload(&p->d_direct_row_pre, p->direct_row_pre);
     rc |= upload(&p->d_tiles1_fb, p->tiles1_fb);
     rc |= upload(&p->d_tiles4_fb, p->tiles4_fb);
     rc |= upload(&p->d_orth_small, p->orth_small);
@@ -528,6 +546,8 @@ int psgd_plan_destroy(psgd_plan* p) {
     cudaFree(p->d_counters);
     cudaFree(p->d_dbg);
     cudaFree(p->d_ctr3);
+    cudaFree(p->d_direct_ids);
+    cudaFree(p->d_direct_row_pre);
     cudaFree(p->d_tiles1_fb);
     cudaFree(p->d_tiles4_fb);
     cudaFree(p->d_orth_small);
@@ -768,7 +788,8 @@ static int p_from_m_impl(psgd_plan* p, float* p_mem, const float* q_mem, int fus
   PhaseScope ts(p, PSGD_PHASE_P_FROM_M, s);
   if (fuse_add ? p->stream1f_now : p->stream1_now) {
     StreamPlan sp{p->d_tasks1, p->d_counters, (int)p->tasks1.size(), p->ring_slot_bytes, p->ring_slots, p->q_bytes, p->d_dbg,
-                  p->d_vtiles, flat, fold ? (int)p->vtiles.size() : 0, fold ? (fuse_add ? 2 : 1) : 0, 1.0f};
+                  p->d_vtiles, flat, fold ? (int)p->vtiles.size() : 0, fold ? (fuse_add ? 2 : 1) : 0, 1.0f,
+                  p->d_direct_ids, p->d_direct_row_pre, (int)p->direct_ids.size()};
     DISPATCH_R(p->R, {
       if (fuse_add) {
         if (!p->attr1f_set) CU(cudaFuncSetAttribute((const void*)k_p_from_m_stream<RR, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->stream_smem));
@@ -920,7 +941,8 @@ static int finalize_impl(psgd_plan* p, const float* p_mem, const float* q_mem, f
   PhaseScope ts(p, PSGD_PHASE_FINALIZE, s);
   if (p->stream4_now) {
     StreamPlan sp{p->d_tasks4, p->d_counters + 2, (int)p->tasks4.size(), p->ring_slot_bytes, p->ring_slots, p->q_bytes, nullptr,
-                  p->d_vtiles, const_cast<float*>(flat), fold ? (int)p->vtiles.size() : 0, fold ? 3 : 0, n_workers};
+                  p->d_vtiles, const_cast<float*>(flat), fold ? (int)p->vtiles.size() : 0, fold ? 3 : 0, n_workers,
+                  p->d_direct_ids, p->d_direct_row_pre, (int)p->direct_ids.size()};
     DISPATCH_R(p->R, {
       if (!p->attr4_set) CU(cudaFuncSetAttribute((const void*)k_finalize_stream<RR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->stream_smem));
       p->attr4_set = true;

@@ -42,7 +42,100 @@ struct StreamPlan {
   int n_vtiles;
   int vec_mode;          // 0 none, 1 pack, 2 pack with grad + err, 3 unpack (/ world)
   float vec_world;
+  // second side job: tiny matrices that do not qualify for the ring (e.g. a 64 x 147 first convolution) are done
+  // straight from global memory by the consumer threads of one CTA each, instead of costing an extra launch
+  const int* direct_ids;
+  const int* direct_row_pre;  // n_direct + 1 prefix sums of their row counts
+  int n_direct;
 };
+
+// The rows of all such matrices form one list of items; warp w of CTA b takes items (k * gridDim + b) * 8 + w, so a
+// 64-row matrix is spread over eight CTAs and costs each of them about a microsecond.
+__device__ __forceinline__ bool direct_item(const StreamPlan& sp, int k, int& mat, int& row) {
+  const int item = (k * (int)gridDim.x + (int)blockIdx.x) * kConsumerWarps + (int)(threadIdx.x >> 5);
+  if (item >= sp.direct_row_pre[sp.n_direct]) return false;
+  int d = 0;
+  while (item >= sp.direct_row_pre[d + 1]) ++d;
+  mat = sp.direct_ids[d];
+  row = item - sp.direct_row_pre[d];
+  return true;
+}
+
+// P = M Q, one row per warp, lanes over the columns, straight from global memory.
+template <int R, bool FUSE>
+__device__ __forceinline__ void direct_p_from_m(const DevPlan& pl, const PtrSlot& ps, const StreamPlan& sp,
+                                                const float* __restrict__ q_mem, float* __restrict__ p_mem, float q_div) {
+  const int lane = threadIdx.x & 31;
+  const int rounds = (sp.direct_row_pre[sp.n_direct] + (int)gridDim.x * kConsumerWarps - 1) / ((int)gridDim.x * kConsumerWarps);
+  for (int k = 0; k < rounds; ++k) {
+    int mat, row;
+    if (!direct_item(sp, k, mat, row)) continue;
+    const MatDesc md = pl.mats[mat];
+    const int m = md.m, r = md.r;
+    const float* Q = q_mem + md.q_off;
+    const float* M = ps.in[mat] + (size_t)row * m;
+    float acc[R];
+#pragma unroll
+    for (int c = 0; c < R; ++c) acc[c] = 0.f;
+    for (int j = lane; j < m; j += 32) {
+      float x;
+      if (FUSE) {
+        x = ps.g[mat][(size_t)row * m + j] + ps.e[mat][(size_t)row * m + j];
+        const_cast<float*>(M)[j] = x;
+      } else {
+        x = M[j];
+      }
+#pragma unroll
+      for (int c = 0; c < R; ++c) {
+        if (c < r) {
+          float q = __ldg(Q + (size_t)j * r + c);
+          if (q_div != 1.0f) q = q / q_div;
+          acc[c] = fmaf(x, q, acc[c]);
+        }
+      }
+    }
+#pragma unroll
+    for (int c = 0; c < R; ++c) {
+      const float t = warp_sum(acc[c]);
+      if (lane == 0 && c < r) p_mem[md.p_off + (size_t)row * r + c] = t;
+    }
+  }
+}
+
+// out = P (Q / world)^T, mem = M - out, one row per warp.
+template <int R>
+__device__ __forceinline__ void direct_finalize(const DevPlan& pl, const PtrSlot& ps, const StreamPlan& sp,
+                                                const float* __restrict__ p_mem, const float* __restrict__ q_mem, float world) {
+  const int lane = threadIdx.x & 31;
+  const int rounds = (sp.direct_row_pre[sp.n_direct] + (int)gridDim.x * kConsumerWarps - 1) / ((int)gridDim.x * kConsumerWarps);
+  for (int k = 0; k < rounds; ++k) {
+    int mat, row;
+    if (!direct_item(sp, k, mat, row)) continue;
+    const MatDesc md = pl.mats[mat];
+    const int m = md.m, r = md.r;
+    const float* Q = q_mem + md.q_off;
+    float p[R];
+#pragma unroll
+    for (int c = 0; c < R; ++c) p[c] = (c < r) ? __ldg(p_mem + md.p_off + (size_t)row * r + c) : 0.f;
+    const float* M = ps.in[mat] + (size_t)row * m;
+    float* Out = ps.out[mat] + (size_t)row * m;
+    float* Mem = ps.mem[mat] + (size_t)row * m;
+    for (int j = lane; j < m; j += 32) {
+      float o = 0.f;
+#pragma unroll
+      for (int c = 0; c < R; ++c) {
+        if (c < r) {
+          float q = __ldg(Q + (size_t)j * r + c);
+          if (world != 1.0f) q = q / world;
+          o = fmaf(p[c], q, o);
+        }
+      }
+      const float x = M[j];
+      Out[j] = o;
+      Mem[j] = x - o;
+    }
+  }
+}
 
 // The flat-buffer gather / scatter of the <=1-D tensors as a side job of a streamed kernel: the consumer threads
 // of CTA b take tiles b, b + gridDim.x, ... (a few KB each) while the producer's first copies are in flight.
@@ -327,6 +420,7 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
   }
 
   if (sp.vec_mode) stream_vec_side_job(sp, ps);
+  if (sp.n_direct) direct_p_from_m<R, FUSE>(pl, ps, sp, q_mem, p_mem, q_div);
   int cur_mat = -1, m = 0, r = 0, pitch = 0;
   float* P = nullptr;
   float* Mw = nullptr;  // FUSE: the send buffer M is written to
@@ -453,6 +547,7 @@ k_finalize_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
   }
 
   if (sp.vec_mode) stream_vec_side_job(sp, ps);
+  if (sp.n_direct) direct_finalize<R>(pl, ps, sp, p_mem, q_mem, world);
   int cur_mat = -1, m = 0, r = 0, pitch = 0;
   const float* P = nullptr;
   float* Out = nullptr;
