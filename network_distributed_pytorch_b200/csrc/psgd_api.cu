@@ -7,6 +7,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/psgd_b200.h"
@@ -72,6 +73,9 @@ struct psgd_plan {
   int n_max = 0;
   std::vector<int> orth_small, orth_tall, orth_generic;  // K2 routing by row count
   int orth_tall_cluster = kOrthCluster;
+  bool pdl = true;              // programmatic dependent launch between the kernels of a step (PSGD_PDL)
+  bool orth_merge = true;       // small matrices ride on the tall launch (PSGD_ORTH_MERGE)
+  int orth_merge_max_ctas = 96;
   bool orth16_attr = false;
   int *d_orth_small = nullptr, *d_orth_tall = nullptr, *d_orth_generic = nullptr;
   size_t smem1 = 0, smem3 = 0, smem4 = 0;
@@ -273,6 +277,35 @@ int set_smem(F* f, size_t bytes) {
   return 0;
 }
 
+// Launch with the optional attributes of this library: thread-block cluster size and programmatic stream
+// serialisation (the kernel may start while its predecessor in the stream drains; see pdl_wait()).
+template <typename... KArgs, typename... Args>
+cudaError_t launch_ex(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s, int cluster, bool pdl,
+                      Args&&... args) {
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute at[2];
+  unsigned na = 0;
+  if (cluster > 1) {
+    at[na].id = cudaLaunchAttributeClusterDimension;
+    at[na].val.clusterDim.x = (unsigned)cluster;
+    at[na].val.clusterDim.y = 1;
+    at[na].val.clusterDim.z = 1;
+    ++na;
+  }
+  if (pdl) {
+    at[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    at[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  cfg.attrs = at;
+  cfg.numAttrs = na;
+  return cudaLaunchKernelEx(&cfg, kernel, std::forward<Args>(args)...);
+}
+
 }  // namespace
 
 extern "C" {
@@ -451,6 +484,9 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
   {  // K2 routing: register-resident single CTA, register-resident cluster, or generic cluster
     const int rpt = R <= 8 ? 4 : 2;
     p->orth_tall_cluster = (R == 16) ? kOrthClusterMax : kOrthCluster;  // R = 16 keeps only 2 rows per thread
+    p->orth_merge = env_ll("PSGD_ORTH_MERGE", 1) != 0;
+    p->pdl = env_ll("PSGD_PDL", 1) != 0;
+    p->orth_merge_max_ctas = (int)env_ll("PSGD_ORTH_MERGE_MAX", 96);
     for (int i = 0; i < n_mat; ++i) {
       const long long nn = p->mats[i].n;
       if (nn == 0 || p->mats[i].m == 0) continue;
@@ -794,11 +830,11 @@ static int p_from_m_impl(psgd_plan* p, float* p_mem, const float* q_mem, int fus
       if (fuse_add) {
         if (!p->attr1f_set) CU(cudaFuncSetAttribute((const void*)k_p_from_m_stream<RR, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->stream_smem));
         p->attr1f_set = true;
-        k_p_from_m_stream<RR, true><<<p->stream_grid, kStreamThreads, p->stream_smem, s>>>(dp, p->slot, sp, q_mem, p_mem, q_div);
+        CU(launch_ex(k_p_from_m_stream<RR, true>, dim3(p->stream_grid), dim3(kStreamThreads), p->stream_smem, s, 1, p->pdl, dp, p->slot, sp, q_mem, p_mem, q_div));
       } else {
         if (!p->attr1_set) CU(cudaFuncSetAttribute((const void*)k_p_from_m_stream<RR, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->stream_smem));
         p->attr1_set = true;
-        k_p_from_m_stream<RR, false><<<p->stream_grid, kStreamThreads, p->stream_smem, s>>>(dp, p->slot, sp, q_mem, p_mem, q_div);
+        CU(launch_ex(k_p_from_m_stream<RR, false>, dim3(p->stream_grid), dim3(kStreamThreads), p->stream_smem, s, 1, p->pdl, dp, p->slot, sp, q_mem, p_mem, q_div));
       }
     });
     if (check_launch("k_p_from_m_stream")) return 1;
@@ -839,13 +875,20 @@ int psgd_orthogonalize(psgd_plan* p, float* p_mem, float n_workers, psgd_stream 
   cudaStream_t s = (cudaStream_t)stream;
   const DevPlan dp = dev_plan(p);
   PhaseScope ts(p, PSGD_PHASE_ORTH, s);
+  // The small matrices (one CTA each) share the launch of the tall ones (one cluster each) when the whole thing
+  // fits a single wave of clusters; a big population of small matrices keeps its own plain launch, where no SM is
+  // lost to cluster placement.
+  const int tcs = p->orth_tall_cluster;
+  const int n_small = (int)p->orth_small.size(), n_tall = (int)p->orth_tall.size();
+  const bool merged = n_tall > 0 && n_small > 0 && p->orth_merge &&
+                      (n_tall + (n_small + tcs - 1) / tcs) * tcs <= p->orth_merge_max_ctas;
   // 1. matrices that fit one CTA's registers: one CTA each, block barriers only
-  if (!p->orth_small.empty()) {
-    const unsigned grid = (unsigned)p->orth_small.size();
+  if (n_small && !merged) {
+    const unsigned grid = (unsigned)n_small;
     if (p->R <= 8) {
-      DISPATCH_R8(p->R, { k_orth_small<RR, 4><<<grid, kOrthSmallThreads, 0, s>>>(dp, p->d_orth_small, p_mem, n_workers); });
+      DISPATCH_R8(p->R, { CU(launch_ex(k_orth_small<RR, 4>, dim3(grid), dim3(kOrthSmallThreads), 0, s, 1, p->pdl, dp, (const int*)p->d_orth_small, p_mem, n_workers)); });
     } else {
-      k_orth_small<16, 2><<<grid, kOrthSmallThreads, 0, s>>>(dp, p->d_orth_small, p_mem, n_workers);
+      CU(launch_ex(k_orth_small<16, 2>, dim3(grid), dim3(kOrthSmallThreads), 0, s, 1, p->pdl, dp, (const int*)p->d_orth_small, p_mem, n_workers));
     }
     if (check_launch("k_orth_small")) return 1;
   }
@@ -854,29 +897,21 @@ int psgd_orthogonalize(psgd_plan* p, float* p_mem, float n_workers, psgd_stream 
     const std::vector<int>& ids = pass == 0 ? p->orth_tall : p->orth_generic;
     const int* d_ids = pass == 0 ? p->d_orth_tall : p->d_orth_generic;
     if (ids.empty()) continue;
-    cudaLaunchConfig_t cfg{};
-    const int csz = pass == 0 ? p->orth_tall_cluster : kOrthCluster;
-    cfg.gridDim = dim3((unsigned)ids.size() * csz);
-    cfg.blockDim = dim3(pass == 0 ? kOrthSmallThreads : kOrthThreads);
-    cfg.dynamicSmemBytes = 0;
-    cfg.stream = s;
-    cudaLaunchAttribute at[1];
-    at[0].id = cudaLaunchAttributeClusterDimension;
-    at[0].val.clusterDim.x = csz;
-    at[0].val.clusterDim.y = 1;
-    at[0].val.clusterDim.z = 1;
-    cfg.attrs = at;
-    cfg.numAttrs = 1;
+    const int csz = pass == 0 ? tcs : kOrthCluster;
+    const int n_ride = (pass == 0 && merged) ? n_small : 0;
+    const dim3 grid((unsigned)(ids.size() + (n_ride + csz - 1) / csz) * csz);
     if (pass == 0) {
+      const int* d_small = p->d_orth_small;
       if (p->R <= 8) {
-        DISPATCH_R8(p->R, { CU(cudaLaunchKernelEx(&cfg, k_orth_tall<RR, 4>, dp, d_ids, p_mem, n_workers)); });
+        DISPATCH_R8(p->R, { CU(launch_ex(k_orth_tall<RR, 4>, grid, dim3(kOrthSmallThreads), 0, s, csz, p->pdl, dp, d_ids, n_tall, d_small, n_ride, p_mem, n_workers)); });
       } else {
         if (!p->orth16_attr) CU(cudaFuncSetAttribute((const void*)k_orth_tall<16, 2>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
         p->orth16_attr = true;
-        CU(cudaLaunchKernelEx(&cfg, k_orth_tall<16, 2>, dp, d_ids, p_mem, n_workers));
+        CU(launch_ex(k_orth_tall<16, 2>, grid, dim3(kOrthSmallThreads), 0, s, csz, p->pdl, dp, d_ids, n_tall, d_small, n_ride, p_mem, n_workers));
       }
     } else {
-      DISPATCH_R(p->R, { CU(cudaLaunchKernelEx(&cfg, k_orthogonalize<RR>, dp, d_ids, p_mem, n_workers)); });
+      // the generic kernel has no dependency wait of its own: plain stream order
+      DISPATCH_R(p->R, { CU(launch_ex(k_orthogonalize<RR>, grid, dim3(kOrthThreads), 0, s, csz, false, dp, d_ids, p_mem, n_workers)); });
     }
     if (check_launch("k_orth_tall")) return 1;
   }
@@ -898,7 +933,7 @@ int psgd_q_from_mt(psgd_plan* p, const float* p_mem, float* q_mem, void* workspa
     const unsigned grid = (unsigned)p->tiles3.size();
     DISPATCH_R(p->R, {
       if (set_smem(k_q_from_mt<RR>, p->smem3)) return 1;
-      k_q_from_mt<RR><<<grid, kThreads, p->smem3, s>>>(dp, p->slot, p_mem, ws, q_mem, fold ? p->d_ctr3 : nullptr);
+      CU(launch_ex(k_q_from_mt<RR>, dim3(grid), dim3(kThreads), p->smem3, s, 1, p->pdl, dp, p->slot, p_mem, (float*)ws, q_mem, fold ? p->d_ctr3 : (int*)nullptr));
     });
     if (check_launch("k_q_from_mt")) return 1;
   }
@@ -946,7 +981,7 @@ static int finalize_impl(psgd_plan* p, const float* p_mem, const float* q_mem, f
     DISPATCH_R(p->R, {
       if (!p->attr4_set) CU(cudaFuncSetAttribute((const void*)k_finalize_stream<RR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->stream_smem));
       p->attr4_set = true;
-      k_finalize_stream<RR><<<p->stream_grid, kStreamThreads, p->stream_smem, s>>>(dp, p->slot, sp, p_mem, q_mem, n_workers);
+      CU(launch_ex(k_finalize_stream<RR>, dim3(p->stream_grid), dim3(kStreamThreads), p->stream_smem, s, 1, p->pdl, dp, p->slot, sp, p_mem, q_mem, n_workers));
     });
     if (check_launch("k_finalize_stream")) return 1;
     if (!p->tiles4_fb.empty()) {

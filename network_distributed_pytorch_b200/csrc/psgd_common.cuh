@@ -77,6 +77,19 @@ struct DevPlan {
   int pad_;
 };
 
+// ---- programmatic dependent launch ------------------------------------------------------
+// The five kernels of a step are launched with programmatic stream serialisation: each lets its successor's CTAs
+// take SMs as they free up (launch latency, barrier set-up, descriptor and first-task fetches happen in the
+// shadow of the predecessor's tail) and every CTA of the successor waits here, before it touches anything a
+// previous kernel of the stream wrote, until the predecessor has completed and flushed.  Both are no-ops for a
+// launch without the attribute.
+__device__ __forceinline__ void pdl_launch_dependents() {
+  asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+}
+__device__ __forceinline__ void pdl_wait() {
+  asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
 // ---- memory helpers -------------------------------------------------------------------
 
 // streaming 128-bit load: read-only path, do not allocate in L1 (M is touched once per pass)

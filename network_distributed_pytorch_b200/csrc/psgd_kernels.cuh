@@ -393,18 +393,37 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
 template <int R, int RPT>
 __global__ void __launch_bounds__(kOrthSmallThreads)
 k_orth_small(DevPlan pl, const int* __restrict__ ids, float* __restrict__ p_mem, float world) {
+  pdl_launch_dependents();
   const MatDesc md = pl.mats[ids[blockIdx.x]];
+  pdl_wait();
   orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, 0, 1);
 }
 
-// one cluster per "tall" matrix (n <= cluster * blockDim * RPT)
+// one cluster per "tall" matrix (n <= cluster * blockDim * RPT).  When the plan also has small matrices and everything
+// fits one wave, they ride on the same launch: the clusters behind the n_tall cooperative ones are mere containers whose
+// CTAs each take one small matrix and never touch the cluster barrier.
 template <int R, int RPT>
 __global__ void __launch_bounds__(kOrthSmallThreads)
-k_orth_tall(DevPlan pl, const int* __restrict__ ids, float* __restrict__ p_mem, float world) {
+k_orth_tall(DevPlan pl, const int* __restrict__ ids, int n_tall, const int* __restrict__ small_ids, int n_small,
+            float* __restrict__ p_mem, float world) {
   cg::cluster_group cluster = cg::this_cluster();
   const int csize = (int)cluster.num_blocks();
-  const MatDesc md = pl.mats[ids[blockIdx.x / csize]];
-  orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, (int)cluster.block_rank(), csize);
+  const int cl = blockIdx.x / csize;
+  pdl_launch_dependents();
+  if (cl < n_tall) {
+    const MatDesc md = pl.mats[ids[cl]];
+    pdl_wait();
+    orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, (int)cluster.block_rank(), csize);
+  } else {
+    const int idx = (cl - n_tall) * csize + (int)cluster.block_rank();
+    if (idx >= n_small) {
+      pdl_wait();  // every CTA waits: the grid must not be able to complete before its predecessor has
+      return;
+    }
+    const MatDesc md = pl.mats[small_ids[idx]];
+    pdl_wait();
+    orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, 0, 1);
+  }
 }
 
 template <int R>
@@ -542,12 +561,15 @@ __global__ void __launch_bounds__(kThreads, 2)
 k_q_from_mt(DevPlan pl, PtrSlot ps, const float* __restrict__ p_mem, float* __restrict__ ws, float* __restrict__ q_mem,
             int* __restrict__ done) {
   extern __shared__ __align__(16) float smem[];
+  pdl_launch_dependents();
   const ColTile t = pl.tiles3[blockIdx.x];
   const MatDesc md = pl.mats[t.mat];
   const float* M = ps.in[t.mat];
   const float* P = p_mem + md.p_off;
+  const unsigned in_flags = ps.flags[t.mat];
+  pdl_wait();
   if (md.cpt == 4) {
-    if (ps.flags[t.mat] & kFlagInVec)
+    if (in_flags & kFlagInVec)
       q_tile<R, 4, true>(md, t, M, P, ws, smem);
     else
       q_tile<R, 4, false>(md, t, M, P, ws, smem);

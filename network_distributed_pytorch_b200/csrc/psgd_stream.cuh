@@ -268,6 +268,7 @@ __device__ __forceinline__ StreamSmem::MatInfo mat_info(const DevPlan& pl, const
 // common prologue: barriers + matrix cache
 __device__ __forceinline__ void stream_setup(const DevPlan& pl, const PtrSlot& ps, const StreamPlan& sp,
                                              const StreamSmem& sm, const float* q_mem) {
+  pdl_launch_dependents();
   if (threadIdx.x == 0) {
     for (int s = 0; s < sp.n_slots; ++s) {
       mbar_init(&sm.full[s], 1);
@@ -288,6 +289,7 @@ __device__ __forceinline__ void stream_setup(const DevPlan& pl, const PtrSlot& p
   __syncthreads();
 }
 
+
 // The producer: one thread takes tasks from the global counter, cuts them into units and refills slots
 // as the consumers release them.  Nothing on its per-unit path touches global memory: the task after
 // the current one is requested while the current one streams.
@@ -298,6 +300,7 @@ __device__ __forceinline__ void stream_producer(const DevPlan& pl, const PtrSlot
   int prev_mat = -1;
   int t = atomicAdd(&sp.counters[0], 1);
   StreamTask task = sp.tasks[t < sp.n_tasks ? t : 0];
+  pdl_wait();  // nothing above depends on an earlier kernel of the stream; the copies below do
   while (t < sp.n_tasks) {
     const int t_next = atomicAdd(&sp.counters[0], 1);  // in flight while this task streams
     const StreamSmem::MatInfo mi = mat_info(pl, ps, sm, q_mem, task.mat);
@@ -419,6 +422,7 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
     return;
   }
 
+  pdl_wait();
   if (sp.vec_mode) stream_vec_side_job(sp, ps);
   if (sp.n_direct) direct_p_from_m<R, FUSE>(pl, ps, sp, q_mem, p_mem, q_div);
   int cur_mat = -1, m = 0, r = 0, pitch = 0;
@@ -546,6 +550,7 @@ k_finalize_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
     return;
   }
 
+  pdl_wait();
   if (sp.vec_mode) stream_vec_side_job(sp, ps);
   if (sp.n_direct) direct_finalize<R>(pl, ps, sp, p_mem, q_mem, world);
   int cur_mat = -1, m = 0, r = 0, pitch = 0;
