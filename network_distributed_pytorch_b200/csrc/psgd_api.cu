@@ -424,8 +424,8 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
   const int wc = std::min(std::max(mmax, 1), p->wc_cap);
   p->smem1 = p->smem4 = (size_t)R * q_pitch(wc, R) * 4;
 
-  const int rows1 = R <= 2 ? 8 : R <= 8 ? 4 : R == 16 ? 2 : 1;
-  const int rows4 = R <= 8 ? 4 : R == 16 ? 2 : 1;
+  const int rows1 = rows_s1(R);
+  const int rows4 = rows_s4(R);
   build_row_tiles(p, p->tiles1, t1_bytes, rows1, true);
   build_row_tiles(p, p->tiles4, t4_bytes, rows4, false);
 

@@ -308,6 +308,85 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
       for (int j = 0; j < R; ++j) v[k][j] *= inv_world;
   }
 
+  // For R <= 8 the step loop stays ROLLED: unrolled, the R steps are R copies of straight-line code that every warp runs exactly
+  // once, and the kernel spent most of its time waiting for instruction fetches (ncu: stall_no_inst 42 % at R = 8,
+  // 160 KB of SASS).  To keep the rows in registers under a runtime step index the columns rotate instead: the column
+  // being normalised is always register 0, the unfinished ones follow, finished ones queue up at the back, and after R
+  // rotations everything is back in place.
+  if constexpr (R <= 8) {
+#pragma unroll 1
+  for (int i = 0; i < R; ++i) {
+    if (i < r) {  // uniform over the CTA / cluster
+      // partial sums of col_i . col_j for all register positions j; one butterfly fold reduces all R of them
+      float s[R];
+#pragma unroll
+      for (int j = 0; j < R; ++j) s[j] = 0.f;
+#pragma unroll
+      for (int k = 0; k < RPT; ++k)
+#pragma unroll
+        for (int j = 0; j < R; ++j) s[j] = fmaf(v[k][0], v[k][j], s[j]);
+      {
+        const float w = warp_fold<R>(s, lane);
+        if ((lane % LPV) == 0) wsum[warp][lane / LPV] = w;
+      }
+      __syncthreads();
+      const int par = i & 1;
+      if (warp == 0) {
+        float t[R];
+#pragma unroll
+        for (int j = 0; j < R; ++j) t[j] = (lane < nwarp) ? wsum[lane][j] : 0.f;
+        const float w = warp_fold<R>(t, lane);
+        if ((lane % LPV) == 0) {
+          const int j = lane / LPV;
+          if (csize > 1) {
+            for (int dst = 0; dst < csize; ++dst) {
+              float* remote = cg::this_cluster().map_shared_rank(&part[0][0][0], dst);
+              remote[(par * kOrthClusterMax + crank) * R + j] = w;
+            }
+          } else {
+            part[par][0][j] = w;
+          }
+        }
+      }
+      if (csize > 1) cg::this_cluster().sync(); else __syncthreads();
+      float tot[R];
+#pragma unroll
+      for (int j = 0; j < R; ++j) tot[j] = 0.f;
+      for (int c = 0; c < csize; ++c) {
+        if (R % 4 == 0) {
+#pragma unroll
+          for (int j = 0; j < R; j += 4) {
+            const float4 q = *reinterpret_cast<const float4*>(&part[par][c][j]);
+            tot[j] += q.x; tot[(j + 1) % R] += q.y; tot[(j + 2) % R] += q.z; tot[(j + 3) % R] += q.w;
+          }
+        } else {
+#pragma unroll
+          for (int j = 0; j < R; ++j) tot[j] += part[par][c][j];
+        }
+      }
+      const float inv = 1.0f / (sqrtf(tot[0]) + 1e-8f);  // eps outside the root, reducer.py:186
+      const int live = R - i;  // positions 1 .. live-1 hold the columns still to be projected
+#pragma unroll
+      for (int k = 0; k < RPT; ++k) {
+        const float vi = v[k][0] * inv;
+        v[k][0] = vi;
+#pragma unroll
+        for (int j = 1; j < R; ++j) {
+          const float upd = fmaf(-(tot[j] * inv), vi, v[k][j]);
+          v[k][j] = (j < live) ? upd : v[k][j];
+        }
+      }
+    }
+#pragma unroll
+    for (int k = 0; k < RPT; ++k) {
+      const float head = v[k][0];
+#pragma unroll
+      for (int j = 0; j + 1 < R; ++j) v[k][j] = v[k][j + 1];
+      v[k][R - 1] = head;
+    }
+  }
+  } else {
+  // R = 16 (2 rows per thread) has no registers to spare for the rotation: unrolled steps
 #pragma unroll
   for (int i = 0; i < R; ++i) {
     if (i < r) {  // uniform over the CTA / cluster
@@ -370,6 +449,7 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
         for (int j = i + 1; j < R; ++j) v[k][j] = fmaf(-coef[j], vi, v[k][j]);
       }
     }
+  }
   }
 #pragma unroll
   for (int k = 0; k < RPT; ++k) {
@@ -454,7 +534,10 @@ k_orthogonalize_one(float* __restrict__ mat, int n, int r) {
 template <int R, int CPT, bool VECLD>
 __device__ __forceinline__ void q_tile(const MatDesc& md, const ColTile& t, const float* __restrict__ M,
                                        const float* __restrict__ P, float* __restrict__ ws, float* smem) {
-  constexpr int U = (R <= 4 && CPT == 4) ? 16 : 8;  // rows in flight per thread (16 x 16 B x 512 threads = 128 KB per SM)
+#ifndef PSGD_K3_U_R8
+#define PSGD_K3_U_R8 8
+#endif
+  constexpr int U = (R <= 4 && CPT == 4) ? 16 : (R == 8 && CPT == 4) ? PSGD_K3_U_R8 : 8;  // rows in flight per thread (16 x 16 B x 512 threads = 128 KB per SM)
   constexpr int NV = CPT * R;
   const int m = md.m, r = md.r, cgw = md.cgw;
   const int RL = kThreads / cgw;

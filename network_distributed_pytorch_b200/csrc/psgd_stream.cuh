@@ -221,8 +221,14 @@ __device__ __forceinline__ void consumer_sync() {  // named barrier over the con
   asm volatile("bar.sync 1, %0;" ::"n"(kConsumerWarps * 32) : "memory");
 }
 
-template <int R> struct RowsS1 { static constexpr int v = (R <= 2) ? 8 : (R <= 8) ? 4 : (R == 16) ? 2 : 1; };
-template <int R> struct RowsS4 { static constexpr int v = (R <= 8) ? 4 : (R == 16) ? 2 : 1; };
+#ifndef PSGD_ROWS1_R8
+#define PSGD_ROWS1_R8 4
+#endif
+// rows of M one consumer warp works on at a time (every Q value read from shared memory is used ROWS times)
+__host__ __device__ constexpr int rows_s1(int R) { return (R <= 2) ? 8 : (R <= 4) ? 4 : (R <= 8) ? PSGD_ROWS1_R8 : (R == 16) ? 2 : 1; }
+__host__ __device__ constexpr int rows_s4(int R) { return (R <= 8) ? 4 : (R == 16) ? 2 : 1; }
+template <int R> struct RowsS1 { static constexpr int v = rows_s1(R); };
+template <int R> struct RowsS4 { static constexpr int v = rows_s4(R); };
 
 // shared memory map: [Q stage | ring slots | full, empty, desc barriers | descriptor per slot | matrix cache]
 struct StreamSmem {
@@ -412,7 +418,8 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
                   float q_div) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   constexpr int ROWS = RowsS1<R>::v;
-  constexpr int NV = ROWS * R;
+  constexpr int RG = (ROWS * R > 32) ? 32 / R : ROWS;  // rows per butterfly fold (at most 32 values)
+  constexpr int NV = RG * R;
   const StreamSmem sm = carve(smem_raw, sp);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   stream_setup(pl, ps, sp, sm, q_mem);
@@ -508,17 +515,20 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
           }
         }
       }
-      float flat[NV];
 #pragma unroll
-      for (int a = 0; a < ROWS; ++a)
+      for (int g = 0; g < ROWS; g += RG) {
+        float flat[NV];
 #pragma unroll
-        for (int c = 0; c < R; ++c) flat[a * R + c] = acc[a][c];
-      const float tot = warp_fold<NV>(flat, lane);
-      constexpr int LPV = 32 / NV;
-      if ((lane % LPV) == 0) {
-        const int idx = lane / LPV;
-        const int a = idx / R, c = idx % R;
-        if (a < nr && c < r) P[(size_t)(u_a + rbase + a) * r + c] = tot;
+        for (int a = 0; a < RG; ++a)
+#pragma unroll
+          for (int c = 0; c < R; ++c) flat[a * R + c] = acc[g + a][c];
+        const float tot = warp_fold<NV>(flat, lane);
+        constexpr int LPV = 32 / NV;
+        if ((lane % LPV) == 0) {
+          const int idx = lane / LPV;
+          const int a = g + idx / R, c = idx % R;
+          if (a < nr && c < r) P[(size_t)(u_a + rbase + a) * r + c] = tot;
+        }
       }
     }
     __syncwarp();
