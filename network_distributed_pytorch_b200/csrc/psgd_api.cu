@@ -158,7 +158,7 @@ DevPlan dev_plan(const psgd_plan* p) {
 
 // rows per tile for the row-streaming kernels (K1, K4)
 void build_row_tiles(const psgd_plan* p, std::vector<int4>& out, long long target_bytes, int rows_per_warp,
-                     bool single_set_when_chunked) {
+                     int chunked_sets) {
   out.clear();
   const int gran = kWarps * rows_per_warp;
   for (int i = 0; i < p->n_mat; ++i) {
@@ -167,7 +167,7 @@ void build_row_tiles(const psgd_plan* p, std::vector<int4>& out, long long targe
     long long t = target_bytes / ((long long)md.m * 4);
     t = (t / gran) * gran;
     if (t < gran) t = gran;
-    if (single_set_when_chunked && md.m > p->wc_cap) t = gran;  // accumulators live across chunks
+    if (md.m > p->wc_cap) t = std::max<long long>(t, chunked_sets * gran);  // a staged Q chunk serves this many row sets
     for (long long r0 = 0; r0 < md.n; r0 += t) {
       const int nr = (int)std::min<long long>(t, md.n - r0);
       out.push_back(make_int4(i, (int)r0, nr, 0));
@@ -351,7 +351,7 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
   const long long t4_bytes = env_ll("PSGD_T4_BYTES", 96 * 1024);
   const long long t3_bytes = env_ll("PSGD_T3_BYTES", 256 * 1024);
   const long long t3_maxblk = env_ll("PSGD_T3_MAXBLK", 48);
-  const int cgw_cap = (int)env_ll("PSGD_T3_CGW", 128);
+  const int cgw_cap = (int)std::min<long long>(env_ll("PSGD_T3_CGW", 128), kThreads3);
 
   p->mats.resize(n_mat);
   long long po = 0, qo = 0, wo = 0;
@@ -396,7 +396,7 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
     md.nblk3 = md.n ? (int)((md.n + t3 - 1) / t3) : 0;
     wo += (long long)md.nblk3 * md.m * md.r;
     wo = (wo + 3) & ~3LL;
-    const int RL = kThreads / cgw;
+    const int RL = kThreads3 / cgw;
     const size_t s3 = ((size_t)md.t3_rows * R + (size_t)RL * md.cpt * R * (cgw + 1)) * 4;
     smem3 = std::max(smem3, s3);
     const int ncol = (int)((groups + cgw - 1) / cgw);
@@ -426,8 +426,9 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
 
   const int rows1 = rows_s1(R);
   const int rows4 = rows_s4(R);
-  build_row_tiles(p, p->tiles1, t1_bytes, rows1, true);
-  build_row_tiles(p, p->tiles4, t4_bytes, rows4, false);
+  const int chunked_sets = (int)std::max<long long>(1, env_ll("PSGD_CHUNKED_SETS", 4));
+  build_row_tiles(p, p->tiles1, t1_bytes, rows1, chunked_sets);
+  build_row_tiles(p, p->tiles4, t4_bytes, rows4, chunked_sets);
 
   {  // streamed path: which matrices qualify, and the shared-memory split between Q stage and ring
     int smem_optin = 232448, sms = 148;
@@ -933,7 +934,7 @@ int psgd_q_from_mt(psgd_plan* p, const float* p_mem, float* q_mem, void* workspa
     const unsigned grid = (unsigned)p->tiles3.size();
     DISPATCH_R(p->R, {
       if (set_smem(k_q_from_mt<RR>, p->smem3)) return 1;
-      CU(launch_ex(k_q_from_mt<RR>, dim3(grid), dim3(kThreads), p->smem3, s, 1, p->pdl, dp, p->slot, p_mem, (float*)ws, q_mem, fold ? p->d_ctr3 : (int*)nullptr));
+      CU(launch_ex(k_q_from_mt<RR>, dim3(grid), dim3(kThreads3), p->smem3, s, 1, p->pdl, dp, p->slot, p_mem, (float*)ws, q_mem, fold ? p->d_ctr3 : (int*)nullptr));
     });
     if (check_launch("k_q_from_mt")) return 1;
   }

@@ -14,6 +14,14 @@ namespace psgd {
 namespace cg = cooperative_groups;
 
 // rows a warp carries at once in K1 / K4 for compile-time rank R
+#ifndef PSGD_K3_THREADS
+#define PSGD_K3_THREADS 256
+#endif
+#ifndef PSGD_K3_MINBLK
+#define PSGD_K3_MINBLK 3
+#endif
+constexpr int kThreads3 = PSGD_K3_THREADS;   // CTA size of K3
+constexpr int kMinBlocks3 = PSGD_K3_MINBLK;  // K3 CTAs per SM the register budget is set for (R <= 8)
 template <int R> struct RowsK1 { static constexpr int v = (R <= 2) ? 8 : (R <= 8) ? 4 : (R == 16) ? 2 : 1; };
 template <int R> struct RowsK4 { static constexpr int v = (R <= 8) ? 4 : (R == 16) ? 2 : 1; };
 
@@ -37,26 +45,23 @@ __device__ __forceinline__ void p_tile(const MatDesc& md, const float* __restric
   const int nchunks = (m + wc_cap - 1) / wc_cap;
   const int pitch = q_pitch(m < wc_cap ? m : wc_cap, R);
 
-  for (int sb = 0; sb < nsets; sb += kWarps) {
-    const int set = sb + warp;
-    const bool live = set < nsets;
-    const int rbase = set * ROWS;  // tile-relative
-    float acc[ROWS][R];
+  // Column chunks outermost: a chunk of Q is staged once per tile and serves all of its row sets.  With more than
+  // one chunk a row's partial sums are added up in P itself, chunk after chunk, by the lane that owns the element
+  // (same warp, same lane every time: program order, no race, fixed order).
+  for (int ch = 0; ch < nchunks; ++ch) {
+    const int c0 = ch * wc_cap;
+    const int wc = (m - c0 < wc_cap) ? (m - c0) : wc_cap;
+    if (ch) __syncthreads();
+    stage_q<R>(Qs, Q, c0, wc, r, pitch, q_div);
+    __syncthreads();
+    const int kmax = wc / V;
+    for (int set = warp; set < nsets; set += kWarps) {
+      const int rbase = set * ROWS;  // tile-relative
+      float acc[ROWS][R];
 #pragma unroll
-    for (int a = 0; a < ROWS; ++a)
+      for (int a = 0; a < ROWS; ++a)
 #pragma unroll
-      for (int c = 0; c < R; ++c) acc[a][c] = 0.f;
-
-    for (int ch = 0; ch < nchunks; ++ch) {
-      const int c0 = ch * wc_cap;
-      const int wc = (m - c0 < wc_cap) ? (m - c0) : wc_cap;
-      if (nchunks > 1 || sb == 0) {  // block-uniform: restage only when the chunk changes
-        if (!(ch == 0 && sb == 0)) __syncthreads();
-        stage_q<R>(Qs, Q, c0, wc, r, pitch, q_div);
-        __syncthreads();
-      }
-      if (!live) continue;
-
+        for (int c = 0; c < R; ++c) acc[a][c] = 0.f;
       size_t roff[ROWS];
 #pragma unroll
       for (int a = 0; a < ROWS; ++a) {
@@ -64,7 +69,6 @@ __device__ __forceinline__ void p_tile(const MatDesc& md, const float* __restric
         if (rr > nrows - 1) rr = nrows - 1;  // clamp: loads stay in bounds, result discarded
         roff[a] = (size_t)(row0 + rr) * m + c0;
       }
-      const int kmax = wc / V;
       for (int k = lane; k < kmax; k += 64) {
         const bool two = (k + 32) < kmax;
         const int k1 = two ? k + 32 : k;
@@ -118,8 +122,6 @@ __device__ __forceinline__ void p_tile(const MatDesc& md, const float* __restric
           }
         }
       }
-    }
-    if (live) {
       float flat[NV];
 #pragma unroll
       for (int a = 0; a < ROWS; ++a)
@@ -130,7 +132,10 @@ __device__ __forceinline__ void p_tile(const MatDesc& md, const float* __restric
       if ((lane % LPV) == 0) {
         const int idx = lane / LPV;
         const int a = idx / R, c = idx % R;
-        if (rbase + a < nrows && c < r) P[(size_t)(row0 + rbase + a) * r + c] = tot;
+        if (rbase + a < nrows && c < r) {
+          float* dst = P + (size_t)(row0 + rbase + a) * r + c;
+          *dst = ch ? *dst + tot : tot;
+        }
       }
     }
   }
@@ -531,16 +536,21 @@ k_orthogonalize_one(float* __restrict__ mat, int n, int r) {
 // combined through shared memory in fixed order and the tile's partial Q goes to the
 // workspace; k_q_reduce sums the row blocks in order (deterministic, no atomics).
 // =======================================================================================
-template <int R, int CPT, bool VECLD>
+template <int R, int CPT, bool VECLD, int NT = kThreads>
 __device__ __forceinline__ void q_tile(const MatDesc& md, const ColTile& t, const float* __restrict__ M,
                                        const float* __restrict__ P, float* __restrict__ ws, float* smem) {
 #ifndef PSGD_K3_U_R8
-#define PSGD_K3_U_R8 8
+#define PSGD_K3_U_R8 6
 #endif
-  constexpr int U = (R <= 4 && CPT == 4) ? 16 : (R == 8 && CPT == 4) ? PSGD_K3_U_R8 : 8;  // rows in flight per thread (16 x 16 B x 512 threads = 128 KB per SM)
+#ifndef PSGD_K3_U_R4
+#define PSGD_K3_U_R4 8
+#endif
+  // rows in flight per thread: 3 CTAs per SM x 256 threads x 8 x 16 B = 96 KB per SM (two CTAs with 16 rows each
+  // measured 1.5 % slower over the step: a third resident CTA hides more of a tile's fixed prologue / epilogue latency)
+  constexpr int U = (R <= 4 && CPT == 4) ? PSGD_K3_U_R4 : (R == 8 && CPT == 4) ? PSGD_K3_U_R8 : 8;
   constexpr int NV = CPT * R;
   const int m = md.m, r = md.r, cgw = md.cgw;
-  const int RL = kThreads / cgw;
+  const int RL = NT / cgw;
   const int tid = threadIdx.x;
   const int cgi = tid % cgw, rl = tid / cgw;
   const int nrows = t.nrows;
@@ -551,7 +561,7 @@ __device__ __forceinline__ void q_tile(const MatDesc& md, const ColTile& t, cons
   {
     const float* src = P + (size_t)t.row0 * r;
     const int total = nrows * R;
-    for (int e = tid; e < total; e += kThreads) {
+    for (int e = tid; e < total; e += NT) {
       const int i = e / R, c = e % R;
       Ps[e] = (c < r) ? __ldg(src + (size_t)i * r + c) : 0.f;
     }
@@ -623,7 +633,7 @@ __device__ __forceinline__ void q_tile(const MatDesc& md, const ColTile& t, cons
   float* dst = ws + md.ws_off + (size_t)t.blk * m * r;
   const int wcols = cgw * CPT;
   const int total = wcols * R;
-  for (int e = tid; e < total; e += kThreads) {
+  for (int e = tid; e < total; e += NT) {
     const int j = e / R, c = e % R;  // tile-relative column, rank index
     const int g = j / CPT, x = j % CPT;
     const int cc = t.col0 + j;
@@ -640,7 +650,7 @@ __device__ __forceinline__ void q_tile(const MatDesc& md, const ColTile& t, cons
 // stage without a second launch.  Which CTA does the summing varies from run to run, the order of the sum does
 // not, so the result stays deterministic.  The counter is left at zero for the next launch.
 template <int R>
-__global__ void __launch_bounds__(kThreads, 2)
+__global__ void __launch_bounds__(kThreads3, (R <= 8) ? kMinBlocks3 : (R == 16) ? 2 : 1)
 k_q_from_mt(DevPlan pl, PtrSlot ps, const float* __restrict__ p_mem, float* __restrict__ ws, float* __restrict__ q_mem,
             int* __restrict__ done) {
   extern __shared__ __align__(16) float smem[];
@@ -653,11 +663,11 @@ k_q_from_mt(DevPlan pl, PtrSlot ps, const float* __restrict__ p_mem, float* __re
   pdl_wait();
   if (md.cpt == 4) {
     if (in_flags & kFlagInVec)
-      q_tile<R, 4, true>(md, t, M, P, ws, smem);
+      q_tile<R, 4, true, kThreads3>(md, t, M, P, ws, smem);
     else
-      q_tile<R, 4, false>(md, t, M, P, ws, smem);
+      q_tile<R, 4, false, kThreads3>(md, t, M, P, ws, smem);
   } else {
-    q_tile<R, 1, false>(md, t, M, P, ws, smem);
+    q_tile<R, 1, false, kThreads3>(md, t, M, P, ws, smem);
   }
   if (done == nullptr) return;
 
@@ -677,7 +687,7 @@ k_q_from_mt(DevPlan pl, PtrSlot ps, const float* __restrict__ p_mem, float* __re
   float* dst = q_mem + md.q_off + e0;
   const int nb = md.nblk3;
   if ((stride & 3) == 0 && (count & 3) == 0) {
-    for (int f = threadIdx.x; f < (count >> 2); f += kThreads) {
+    for (int f = threadIdx.x; f < (count >> 2); f += kThreads3) {
       float4 sum = make_float4(0.f, 0.f, 0.f, 0.f);
       int b = 0;
       for (; b + 4 <= nb; b += 4) {
@@ -697,7 +707,7 @@ k_q_from_mt(DevPlan pl, PtrSlot ps, const float* __restrict__ p_mem, float* __re
       dst[4 * f] = sum.x; dst[4 * f + 1] = sum.y; dst[4 * f + 2] = sum.z; dst[4 * f + 3] = sum.w;
     }
   } else {
-    for (int e = threadIdx.x; e < count; e += kThreads) {
+    for (int e = threadIdx.x; e < count; e += kThreads3) {
       float sum = 0.f;
       for (int b = 0; b < nb; ++b) sum += __ldcg(src + (size_t)b * stride + e);
       dst[e] = sum;

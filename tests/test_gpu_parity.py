@@ -124,7 +124,7 @@ SHAPE_SETS = {
     "odd_columns": [(64, 3, 7, 7), (64,), (33, 27), (5,), (130, 1), (1, 130), (7, 13), (2,)],
     "transformer_slice": [(512, 768), (768,), (768, 768), (768,), (3072, 768), (3072,), (768, 3072), (2, 768), (2,)],
     "tall": [(30522, 64), (64,), (4099, 132), (1,)],
-    "wide_chunked": [(9, 25088), (9,), (40, 30000), (3,), (70, 13001), (2,)],
+    "wide_chunked": [(9, 25088), (9,), (40, 30000), (3,), (70, 13001), (2,), (300, 8200), (300,)],
     "conv": [(128, 64, 3, 3), (128,), (256, 128, 1, 1), (256,), (512, 512, 3, 3), (512,), (1000, 512), (1000,)],
 }
 
