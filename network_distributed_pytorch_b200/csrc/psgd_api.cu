@@ -426,9 +426,24 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
 
   const int rows1 = rows_s1(R);
   const int rows4 = rows_s4(R);
-  const int chunked_sets = (int)std::max<long long>(1, env_ll("PSGD_CHUNKED_SETS", 4));
-  build_row_tiles(p, p->tiles1, t1_bytes, rows1, chunked_sets);
-  build_row_tiles(p, p->tiles4, t4_bytes, rows4, chunked_sets);
+  // Matrices whose Q does not fit the stage in one piece: a staged chunk should serve several row sets (up to 4 per
+  // warp), as long as that still leaves a tile per SM for their launch.
+  auto chunked_sets_for = [&](int rows_per_warp) {
+    const long long forced = env_ll("PSGD_CHUNKED_SETS", 0);
+    if (forced > 0) return (int)forced;
+    int sms = 148;
+    if (device >= 0) cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+    for (int sets = 4; sets > 1; sets /= 2) {
+      long long tiles = 0;
+      const long long t = (long long)sets * kWarps * rows_per_warp;
+      for (int i = 0; i < n_mat; ++i)
+        if (p->mats[i].m > p->wc_cap && p->mats[i].n > 0) tiles += (p->mats[i].n + t - 1) / t;
+      if (tiles >= sms) return sets;
+    }
+    return 1;
+  };
+  build_row_tiles(p, p->tiles1, t1_bytes, rows1, chunked_sets_for(rows1));
+  build_row_tiles(p, p->tiles4, t4_bytes, rows4, chunked_sets_for(rows4));
 
   {  // streamed path: which matrices qualify, and the shared-memory split between Q stage and ring
     int smem_optin = 232448, sms = 148;
