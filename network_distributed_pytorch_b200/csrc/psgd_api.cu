@@ -73,6 +73,7 @@ struct psgd_plan {
   int n_max = 0;
   std::vector<int> orth_small, orth_tall, orth_generic;  // K2 routing by row count
   int orth_tall_cluster = kOrthCluster;
+  int split_max_sub = 0;        // K1: column-split units with at most this many row groups (PSGD_SPLIT_MAX_SUB, 0..3)
   bool pdl = true;              // programmatic dependent launch between the kernels of a step (PSGD_PDL)
   bool orth_merge = true;       // small matrices ride on the tall launch (PSGD_ORTH_MERGE)
   int orth_merge_max_ctas = 96;
@@ -98,6 +99,7 @@ struct psgd_plan {
   int4* d_tiles1_fb = nullptr;
   int4* d_tiles4_fb = nullptr;
   int stream_grid = 148, ring_slot_bytes = 0, ring_slots = 0, q_bytes = 0;
+  int ring_slot_bytes1 = 0, ring_slots1 = 0;  // K1's own ring geometry (same shared-memory budget)
   size_t stream_smem = 0;
   bool attr1_set = false, attr1f_set = false, attr4_set = false;  // opt-in shared memory size set on the streamed kernels
   // device tables
@@ -179,7 +181,7 @@ void build_row_tiles(const psgd_plan* p, std::vector<int4>& out, long long targe
 // each, with guided-self-scheduling sizes (about remaining / (2 * CTAs) bytes, never below
 // `min_units`).  The largest matrix goes last so that the fine-grained tail of the schedule stays inside
 // one matrix (one Q stage per CTA).
-void build_stream_tasks(const psgd_plan* p, int rows_per_sub, std::vector<StreamTask>& tasks) {
+void build_stream_tasks(const psgd_plan* p, int rows_per_sub, int slot_bytes, std::vector<StreamTask>& tasks) {
   tasks.clear();
   // smallest matrices first, largest last: the long head tasks cover the many small matrices (one Q stage
   // each), the fine-grained tail of the schedule walks through the few largest ones
@@ -201,7 +203,7 @@ void build_stream_tasks(const psgd_plan* p, int rows_per_sub, std::vector<Stream
   for (int i : order) {
     const MatDesc& md = p->mats[i];
     const long long row_bytes = (long long)md.m * 4;
-    const int rpu = (int)std::max<long long>(1, p->ring_slot_bytes / row_bytes);
+    const int rpu = (int)std::max<long long>(1, slot_bytes / row_bytes);
     const int sub_per_unit = (rpu + rows_per_sub - 1) / rows_per_sub;
     int row = 0;
     while (row < md.n) {
@@ -455,13 +457,15 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
     const long long q_cap = env_ll("PSGD_STREAM_QCAP", 100 * 1024);
     long long slot = env_ll("PSGD_SLOT_BYTES", 48 * 1024);
     slot = std::max<long long>(1024, (slot / 128) * 128);
+    long long slot1 = env_ll("PSGD_SLOT1_BYTES", slot);
+    slot1 = std::max<long long>(1024, (slot1 / 128) * 128);
     p->eligible.assign(n_mat, 0);
     long long qb = 0;
     if (env_ll("PSGD_STREAM", 1) != 0) {
       for (int i = 0; i < n_mat; ++i) {
         const MatDesc& md = p->mats[i];
         const long long qs = (long long)R * q_pitch(md.m, R) * 4;
-        if (md.n > 0 && md.m > 0 && md.m % 4 == 0 && (long long)md.m * 4 <= slot && qs <= q_cap) {
+        if (md.n > 0 && md.m > 0 && md.m % 4 == 0 && (long long)md.m * 4 <= std::min(slot, slot1) && qs <= q_cap) {
           p->eligible[i] = 1;
           qb = std::max(qb, qs);
         }
@@ -469,15 +473,22 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
     }
     qb = (qb + 127) & ~127LL;
     const long long ring = (long long)smem_optin - qb - kStreamSmemExtra - 128;
-    const int slots = (int)std::min<long long>(kMaxSlots, ring / slot);
+    const int slots = (int)std::min<long long>(kMaxSlots, ring / (slot + kPartBytes));
     if (qb > 0 && slots >= 2) {
       p->stream_ok = true;
       p->ring_slot_bytes = (int)slot;
       p->ring_slots = slots;
       p->q_bytes = (int)qb;
-      p->stream_smem = (size_t)qb + (size_t)slots * slot + kStreamSmemExtra;
-      build_stream_tasks(p, rows1, p->tasks1);
-      build_stream_tasks(p, rows4, p->tasks4);
+      p->stream_smem = (size_t)qb + (size_t)slots * slot + kStreamSmemExtra + (size_t)slots * kPartBytes;
+      p->ring_slot_bytes1 = (int)slot1;
+      p->ring_slots1 = (int)std::min<long long>(kMaxSlots, ring / (slot1 + kPartBytes));
+      if (p->ring_slots1 < 2) {
+        p->ring_slot_bytes1 = (int)slot;
+        p->ring_slots1 = slots;
+      }
+      p->stream_smem = std::max(p->stream_smem, (size_t)qb + (size_t)p->ring_slots1 * (p->ring_slot_bytes1 + kPartBytes) + kStreamSmemExtra);
+      build_stream_tasks(p, rows1, p->ring_slot_bytes1, p->tasks1);
+      build_stream_tasks(p, rows4, p->ring_slot_bytes, p->tasks4);
       // tiny matrices that do not qualify ride on the streamed launch as a side job; the rest get their own launch
       std::vector<char> side(n_mat, 0);
       const long long side_max = env_ll("PSGD_SIDE_MAX_ELEMS", 64 * 1024);
@@ -502,6 +513,9 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
     p->orth_tall_cluster = (R == 16) ? kOrthClusterMax : kOrthCluster;  // R = 16 keeps only 2 rows per thread
     p->orth_merge = env_ll("PSGD_ORTH_MERGE", 1) != 0;
     p->pdl = env_ll("PSGD_PDL", 1) != 0;
+    // measured: pays at R >= 8 (twice the FMAs per byte: DistilBERT r=8 step 291 -> 284 us), costs 1-3 % at R <= 4
+    // where one warp per unit already keeps up with the ring
+    p->split_max_sub = (int)std::min<long long>(3, std::max<long long>(0, env_ll("PSGD_SPLIT_MAX_SUB", R >= 8 ? 2 : 0)));
     p->orth_merge_max_ctas = (int)env_ll("PSGD_ORTH_MERGE_MAX", 96);
     for (int i = 0; i < n_mat; ++i) {
       const long long nn = p->mats[i].n;
@@ -839,9 +853,9 @@ static int p_from_m_impl(psgd_plan* p, float* p_mem, const float* q_mem, int fus
   const unsigned grid = (unsigned)p->tiles1.size();
   PhaseScope ts(p, PSGD_PHASE_P_FROM_M, s);
   if (fuse_add ? p->stream1f_now : p->stream1_now) {
-    StreamPlan sp{p->d_tasks1, p->d_counters, (int)p->tasks1.size(), p->ring_slot_bytes, p->ring_slots, p->q_bytes, p->d_dbg,
+    StreamPlan sp{p->d_tasks1, p->d_counters, (int)p->tasks1.size(), p->ring_slot_bytes1, p->ring_slots1, p->q_bytes, p->d_dbg,
                   p->d_vtiles, flat, fold ? (int)p->vtiles.size() : 0, fold ? (fuse_add ? 2 : 1) : 0, 1.0f,
-                  p->d_direct_ids, p->d_direct_row_pre, (int)p->direct_ids.size()};
+                  p->d_direct_ids, p->d_direct_row_pre, (int)p->direct_ids.size(), p->split_max_sub};
     DISPATCH_R(p->R, {
       if (fuse_add) {
         if (!p->attr1f_set) CU(cudaFuncSetAttribute((const void*)k_p_from_m_stream<RR, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->stream_smem));
@@ -993,7 +1007,7 @@ static int finalize_impl(psgd_plan* p, const float* p_mem, const float* q_mem, f
   if (p->stream4_now) {
     StreamPlan sp{p->d_tasks4, p->d_counters + 2, (int)p->tasks4.size(), p->ring_slot_bytes, p->ring_slots, p->q_bytes, nullptr,
                   p->d_vtiles, const_cast<float*>(flat), fold ? (int)p->vtiles.size() : 0, fold ? 3 : 0, n_workers,
-                  p->d_direct_ids, p->d_direct_row_pre, (int)p->direct_ids.size()};
+                  p->d_direct_ids, p->d_direct_row_pre, (int)p->direct_ids.size(), 0};
     DISPATCH_R(p->R, {
       if (!p->attr4_set) CU(cudaFuncSetAttribute((const void*)k_finalize_stream<RR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->stream_smem));
       p->attr4_set = true;

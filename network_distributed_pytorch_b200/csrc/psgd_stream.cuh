@@ -47,6 +47,7 @@ struct StreamPlan {
   const int* direct_ids;
   const int* direct_row_pre;  // n_direct + 1 prefix sums of their row counts
   int n_direct;
+  int split_max_sub;     // K1: units with at most this many row groups are also cut by columns (0: never)
 };
 
 // The rows of all such matrices form one list of items; warp w of CTA b takes items (k * gridDim + b) * 8 + w, so a
@@ -221,6 +222,12 @@ __device__ __forceinline__ void consumer_sync() {  // named barrier over the con
   asm volatile("bar.sync 1, %0;" ::"n"(kConsumerWarps * 32) : "memory");
 }
 
+#ifndef PSGD_K1_UNROLL_R4
+#define PSGD_K1_UNROLL_R4 2
+#endif
+#ifndef PSGD_K1_UNROLL_R8
+#define PSGD_K1_UNROLL_R8 2
+#endif
 #ifndef PSGD_ROWS1_R8
 #define PSGD_ROWS1_R8 4
 #endif
@@ -230,18 +237,23 @@ __host__ __device__ constexpr int rows_s4(int R) { return (R <= 8) ? 4 : (R == 1
 template <int R> struct RowsS1 { static constexpr int v = rows_s1(R); };
 template <int R> struct RowsS4 { static constexpr int v = rows_s4(R); };
 
-// shared memory map: [Q stage | ring slots | full, empty, desc barriers | descriptor per slot | matrix cache]
+// shared memory map: [Q stage | ring slots | full, empty, desc, partial barriers | descriptor per slot | matrix cache |
+// partial sums of column-split units]
 struct StreamSmem {
   float* qs;
   unsigned char* ring;
   uint64_t* full;   // data of the slot has landed (tx bytes)
   uint64_t* empty;  // all consumer warps are done with the slot
   uint64_t* desc;   // the slot's descriptor is published (well before its data lands)
+  uint64_t* pbar;   // K1, column-split units: every consumer warp has delivered its partial sums of the slot's unit
   volatile int4* slot_desc;
   struct MatInfo { const float* base; const float* q; const float* g; const float* e; int m; int r; long long pad; };
   MatInfo* matinfo;
+  float* part;      // K1, column-split units: [slot][item][32] partial sums
 };
-constexpr int kStreamSmemExtra = 3 * kMaxSlots * 8 + kMaxSlots * 16 + kMatCache * 48;
+constexpr int kSplitItems = 12;                  // most (row group, column slice) items of a column-split unit
+constexpr int kPartBytes = kSplitItems * 32 * 4;  // per ring slot
+constexpr int kStreamSmemExtra = 4 * kMaxSlots * 8 + kMaxSlots * 16 + kMatCache * 48;  // + n_slots * kPartBytes
 static_assert(sizeof(StreamSmem::MatInfo) == 48, "MatInfo layout");
 
 __device__ __forceinline__ StreamSmem carve(unsigned char* base, const StreamPlan& sp) {
@@ -251,8 +263,10 @@ __device__ __forceinline__ StreamSmem carve(unsigned char* base, const StreamPla
   s.full = reinterpret_cast<uint64_t*>(base + sp.q_bytes + (size_t)sp.n_slots * sp.slot_bytes);
   s.empty = s.full + kMaxSlots;
   s.desc = s.empty + kMaxSlots;
-  s.slot_desc = reinterpret_cast<volatile int4*>(s.desc + kMaxSlots);
+  s.pbar = s.desc + kMaxSlots;
+  s.slot_desc = reinterpret_cast<volatile int4*>(s.pbar + kMaxSlots);
   s.matinfo = reinterpret_cast<StreamSmem::MatInfo*>(const_cast<int4*>(s.slot_desc) + kMaxSlots);
+  s.part = reinterpret_cast<float*>(s.matinfo + kMatCache);
   return s;
 }
 
@@ -280,6 +294,7 @@ __device__ __forceinline__ void stream_setup(const DevPlan& pl, const PtrSlot& p
       mbar_init(&sm.full[s], 1);
       mbar_init(&sm.empty[s], kConsumerWarps);
       mbar_init(&sm.desc[s], 1);
+      mbar_init(&sm.pbar[s], kConsumerWarps);
     }
     mbar_fence_init();
   }
@@ -419,6 +434,7 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
   extern __shared__ __align__(128) unsigned char smem_raw[];
   constexpr int ROWS = RowsS1<R>::v;
   constexpr int RG = (ROWS * R > 32) ? 32 / R : ROWS;  // rows per butterfly fold (at most 32 values)
+  constexpr int UNR1 = (R <= 4) ? PSGD_K1_UNROLL_R4 : PSGD_K1_UNROLL_R8;  // column steps in flight per warp
   constexpr int NV = RG * R;
   const StreamSmem sm = carve(smem_raw, sp);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -433,6 +449,7 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
   if (sp.vec_mode) stream_vec_side_job(sp, ps);
   if (sp.n_direct) direct_p_from_m<R, FUSE>(pl, ps, sp, q_mem, p_mem, q_div);
   int cur_mat = -1, m = 0, r = 0, pitch = 0;
+  unsigned pphase = 0;  // bit s: parity of the partial barrier of slot s
   float* P = nullptr;
   float* Mw = nullptr;  // FUSE: the send buffer M is written to
   const bool dbg = sp.dbg != nullptr && threadIdx.x == 0;
@@ -467,20 +484,32 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
       continue;
     }
     const int nsub = (u_n + ROWS - 1) / ROWS;
-    // sub-span j of this unit belongs to warp (rot + j) % kConsumerWarps.  Every warp arrives on every
-    // unit, with or without a sub-span: that keeps any slot's barriers within one lap of every warp (a
-    // warp that skipped arrivals could find a slot two laps ahead and mis-read the parity).
+    const int kmax = m >> 2;
+    // Work items of a unit.  Normally one item = ROWS rows x all columns (sub-span j belongs to warp (rot + j) %
+    // kConsumerWarps).  A wide matrix puts only a few rows into a unit and would keep one or two warps busy, so there
+    // the columns are cut into `cs` slices as well: the warps leave their partial sums in shared memory, arrive on the
+    // slot's partial barrier WITHOUT waiting and move on; only the warp that owns the last slice of a row group waits
+    // for the barrier, adds the slices up in slice order and writes P (deterministic, no full-CTA barrier per unit).
+    int cs = 1;
+    if (nsub <= sp.split_max_sub)
+      while (nsub * cs < kConsumerWarps && (kmax >> 6) >= cs) cs <<= 1;  // a slice keeps >= 32 float4 columns
+    const int nitems = nsub * cs;
+    // Every warp arrives on every unit, with or without an item: that keeps any slot's barriers within one lap of
+    // every warp (a warp that skipped arrivals could find a slot two laps ahead and mis-read the parity).
     const int j0 = (warp - u_w % kConsumerWarps + kConsumerWarps) % kConsumerWarps;
-    if (j0 >= nsub) {
+    if (j0 >= nitems && cs == 1) {
       if (lane == 0) mbar_arrive(&sm.empty[slot]);
       continue;
     }
     if (dbg) c0 = clock64();
-    mbar_wait(&sm.full[slot], phase);
+    if (j0 < nitems) mbar_wait(&sm.full[slot], phase);
     if (dbg) { d_data += clock64() - c0; ++d_units; c0 = clock64(); }
-    const int kmax = m >> 2;
-    for (int j = j0; j < nsub; j += kConsumerWarps) {
-      const int rbase = j * ROWS;
+    const int kslice = (kmax + cs - 1) / cs;
+    for (int j = j0; j < nitems; j += kConsumerWarps) {
+      const int sub = j / cs;
+      const int k_lo = (j - sub * cs) * kslice;
+      const int k_hi = (k_lo + kslice < kmax) ? k_lo + kslice : kmax;
+      const int rbase = sub * ROWS;
       const int nr = (u_n - rbase < ROWS) ? (u_n - rbase) : ROWS;
       const float* rowp[ROWS];
 #pragma unroll
@@ -490,8 +519,8 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
       for (int a = 0; a < ROWS; ++a)
 #pragma unroll
         for (int c = 0; c < R; ++c) acc[a][c] = 0.f;
-#pragma unroll 2
-      for (int k = lane; k < kmax; k += 32) {
+#pragma unroll(UNR1)
+      for (int k = k_lo + lane; k < k_hi; k += 32) {
         float4 x[ROWS];
 #pragma unroll
         for (int a = 0; a < ROWS; ++a) x[a] = *reinterpret_cast<const float4*>(rowp[a] + 4 * k);
@@ -527,9 +556,29 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
         if ((lane % LPV) == 0) {
           const int idx = lane / LPV;
           const int a = g + idx / R, c = idx % R;
-          if (a < nr && c < r) P[(size_t)(u_a + rbase + a) * r + c] = tot;
+          if (cs == 1) {
+            if (a < nr && c < r) P[(size_t)(u_a + rbase + a) * r + c] = tot;
+          } else {
+            sm.part[(slot * kSplitItems + j) * 32 + g * R + idx] = tot;
+          }
         }
       }
+    }
+    if (cs > 1) {
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&sm.pbar[slot]);
+      for (int sub = 0; sub < nsub; ++sub) {
+        if (warp != (u_w + sub * cs + cs - 1) % kConsumerWarps) continue;
+        mbar_wait(&sm.pbar[slot], (pphase >> slot) & 1u);
+        if (lane < ROWS * R) {
+          const float* pp = sm.part + (slot * kSplitItems + sub * cs) * 32 + lane;
+          float t = pp[0];
+          for (int sl = 1; sl < cs; ++sl) t += pp[sl * 32];
+          const int a = lane / R, c = lane % R;
+          if (sub * ROWS + a < u_n && c < r) P[(size_t)(u_a + sub * ROWS + a) * r + c] = t;
+        }
+      }
+      pphase ^= 1u << slot;
     }
     __syncwarp();
     if (lane == 0) mbar_arrive(&sm.empty[slot]);
