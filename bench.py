@@ -378,10 +378,33 @@ def run_b200(args):
         if world > 1:
             dist.all_reduce(ems, op=dist.ReduceOp.MAX)
         ems = float(ems.item()) / E
+
+        # what the link alone allows: both copies of one step running concurrently, nothing else
+        def duplex_ms(reps=4):
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            torch.cuda.synchronize(dev)
+            a.record(s_main)
+            for _ in range(reps):
+                s_h2d.wait_stream(s_main)
+                s_d2h.wait_stream(s_main)
+                with torch.cuda.stream(s_h2d):
+                    ins[1].copy_(host_in, non_blocking=True)
+                with torch.cuda.stream(s_d2h):
+                    host_out.copy_(outs[1], non_blocking=True)
+                s_main.wait_stream(s_h2d)
+                s_main.wait_stream(s_d2h)
+            b.record(s_main)
+            torch.cuda.synchronize(dev)
+            return a.elapsed_time(b) / reps
+
+        link_ms = duplex_ms()
         e2e = {"value": world * st["grad_bytes"] / (ems * 1e-3) / 1e9, "unit": UNIT, "ms_per_step": ems,
                "steps": E, "h2d_bytes_per_step": total * 4, "d2h_bytes_per_step": total * 4,
                "path": "per step: pinned host -> HBM copy of all gradients, PowerSGDReducer.reduce(), grad_out HBM -> "
-                       "pinned host; copies of neighbouring steps overlap on the two copy engines"}
+                       "pinned host; copies of neighbouring steps overlap on the two copy engines",
+               "link_only_ms_per_step": link_ms,
+               "link_note": "the same two copies (H2D + D2H of one step, concurrently) with no kernel running: the floor "
+                            "the host link sets for ms_per_step"}
     # ---- training samples/sec (BASELINE.json metric, second half): the upstream loop on synthetic tokens ----
     training = None
     if not args.skip_train and args.workload in ("distilbert", "bert-large", "resnet18", "resnet50"):
