@@ -38,7 +38,7 @@ def parse():
     ap.add_argument("--rank", type=int, default=4, help="PowerSGD compression rank")
     ap.add_argument("--no-reuse-query", action="store_true")
     ap.add_argument("--extra-power-iterations", type=int, default=0)
-    ap.add_argument("--e2e-steps", type=int, default=10)
+    ap.add_argument("--e2e-steps", type=int, default=40)  # long enough that pipeline fill and drain (one copy each) are ~2 %
     ap.add_argument("--cpu-reps", type=int, default=5)
     ap.add_argument("--skip-cpu-baseline", action="store_true")
     ap.add_argument("--skip-e2e", action="store_true")
