@@ -353,7 +353,7 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
   const long long t4_bytes = env_ll("PSGD_T4_BYTES", 96 * 1024);
   const long long t3_bytes = env_ll("PSGD_T3_BYTES", 256 * 1024);
   const long long t3_maxblk = env_ll("PSGD_T3_MAXBLK", 48);
-  const int cgw_cap = (int)std::min<long long>(env_ll("PSGD_T3_CGW", 128), kThreads3);
+  const int cgw_cap = (int)std::min<long long>(env_ll("PSGD_T3_CGW", 64), kThreads3);
 
   p->mats.resize(n_mat);
   long long po = 0, qo = 0, wo = 0;
