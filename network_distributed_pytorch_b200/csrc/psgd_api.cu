@@ -1312,6 +1312,29 @@ int psgd_peer_allreduce(const void* const* peer_in, void* const* peer_signal, fl
   return check_launch("k_peer_allreduce");
 }
 
+int psgd_peer_allreduce_mc(const void* const* peer_in, void* const* peer_signal, void* multicast, float* out, int64_t n,
+                           int rank, int world, int slot0, uint32_t epoch, int device, psgd_stream stream) {
+  if (world < 1 || world > kMaxPeers) return fail("psgd_peer_allreduce_mc: world size %d not in 1..%d", world, kMaxPeers);
+  if (rank < 0 || rank >= world) return fail("psgd_peer_allreduce_mc: bad rank");
+  if (n < 0 || !peer_in || !peer_signal || !multicast || (n && !out)) return fail("psgd_peer_allreduce_mc: bad argument");
+  if (n == 0) return 0;
+  PeerArgs a{};
+  for (int r = 0; r < world; ++r) {
+    if (!peer_in[r] || !peer_signal[r]) return fail("psgd_peer_allreduce_mc: rank %d has a null buffer", r);
+    a.in[r] = (const float*)peer_in[r];
+    a.sig[r] = (unsigned*)peer_signal[r];
+  }
+  if (((uintptr_t)peer_in[rank] | (uintptr_t)multicast | (uintptr_t)out) & 15)
+    return fail("psgd_peer_allreduce_mc: buffers must be 16-byte aligned");
+  CU(cudaSetDevice(device));
+  cudaStream_t s = (cudaStream_t)stream;
+  const long long n4 = (n + 3) / 4;
+  // every CTA takes part in both flag barriers, so the grid must be resident at once: at most one CTA per SM
+  const unsigned grid = (unsigned)std::min<long long>(128, std::max<long long>(1, (n4 + kThreads - 1) / kThreads));
+  k_peer_allreduce_mc<<<grid, kThreads, 0, s>>>(a, (float*)multicast, out, (long long)n, rank, world, slot0, epoch);
+  return check_launch("k_peer_allreduce_mc");
+}
+
 int psgd_orthogonalize_one(float* mat, int64_t n, int r, int device, psgd_stream stream) {
   if (n < 0 || r < 0) return fail("psgd_orthogonalize_one: negative shape");
   if (n == 0 || r == 0) return 0;

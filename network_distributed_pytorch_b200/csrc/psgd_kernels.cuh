@@ -1034,4 +1034,79 @@ k_peer_allreduce(PeerArgs a, float* __restrict__ out, long long n, int rank, int
   }
 }
 
+
+// ---- the same sum through the NVSwitch multicast address of the symmetric buffer ----------------------------
+// Two-shot, in place: after a flag barrier ("every rank's input is written") rank k owns the k-th slice of the
+// buffer: one multimem.ld_reduce returns the switch-side sum of all ranks' copies of an element, one multimem.st
+// writes it back into every rank's copy.  A second flag barrier ("every rank's slice is stored everywhere") and the
+// result is copied from this rank's copy to `out`.  Each element is summed exactly once, so all ranks hold the
+// same bits; a rank moves n/W elements over NVLink instead of (W-1) n.
+__device__ unsigned g_mc_blocks_done;
+
+__device__ __forceinline__ float4 mm_ld_reduce4(const float* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+__device__ __forceinline__ void mm_st4(float* mc, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w) : "memory");
+}
+
+// all threads of the CTA return once every rank has posted `epoch` in this rank's flags[0 .. world)
+__device__ __forceinline__ void peer_flags_wait(const unsigned* flags, int world, unsigned epoch, int rank, int which) {
+  if ((int)threadIdx.x < world) {
+    const long long t0 = clock64();
+    while ((int)(ld_acquire_sys(flags + threadIdx.x) - epoch) < 0) {
+      if (clock64() - t0 > 20000000000LL) {  // ~10 s: a crashed peer must not hang the GPU
+        printf("psgd k_peer_allreduce_mc: rank %d timed out waiting for rank %d (barrier %d, epoch %u)\n", rank,
+               (int)threadIdx.x, which, epoch);
+        __trap();
+      }
+    }
+  }
+  __syncthreads();
+}
+
+__global__ void __launch_bounds__(kThreads)
+k_peer_allreduce_mc(PeerArgs a, float* __restrict__ mc, float* __restrict__ out, long long n, int rank, int world,
+                    int slot0, unsigned epoch) {
+  __shared__ int s_last;
+  const long long n4 = (n + 3) >> 2;  // the symmetric buffers are padded to whole float4s, `out` is not
+  if (blockIdx.x == 0 && (int)threadIdx.x < world) {
+    __threadfence_system();
+    st_release_sys(a.sig[threadIdx.x] + slot0 + rank, epoch);  // this rank's input is complete (stream order)
+  }
+  peer_flags_wait(a.sig[rank] + slot0, world, epoch, rank, 0);
+
+  const long long per = (n4 + world - 1) / world;
+  const long long lo = (long long)rank * per;
+  const long long hi = (lo + per < n4) ? lo + per : n4;
+  const long long stride = (long long)gridDim.x * kThreads;
+  for (long long i = lo + (long long)blockIdx.x * kThreads + threadIdx.x; i < hi; i += stride) {
+    const float4 v = mm_ld_reduce4(mc + 4 * i);
+    mm_st4(mc + 4 * i, v);
+  }
+  __threadfence_system();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = (atomicAdd(&g_mc_blocks_done, 1u) == gridDim.x - 1);
+  __syncthreads();
+  if (s_last) {  // the whole slice of this rank is stored in every copy
+    if (threadIdx.x == 0) g_mc_blocks_done = 0;
+    if ((int)threadIdx.x < world) {
+      __threadfence_system();
+      st_release_sys(a.sig[threadIdx.x] + slot0 + kMaxPeers + rank, epoch);
+    }
+  }
+  peer_flags_wait(a.sig[rank] + slot0 + kMaxPeers, world, epoch, rank, 1);
+
+  const float* mine = a.in[rank];
+  const long long full4 = n >> 2;
+  for (long long i = (long long)blockIdx.x * kThreads + threadIdx.x; i < full4; i += stride)
+    reinterpret_cast<float4*>(out)[i] = ld_sys4(mine + 4 * i);
+  for (long long i = (full4 << 2) + (long long)blockIdx.x * kThreads + threadIdx.x; i < n; i += stride)
+    out[i] = ld_sys1(mine + i);
+}
+
 }  // namespace psgd

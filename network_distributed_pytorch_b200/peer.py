@@ -34,10 +34,15 @@ class PeerExchange:
                     symm.empty(pad4(n_q), dtype=torch.float32, device=device)]
         self.hdl = [symm.rendezvous(b, group) for b in self.buf]
         for h in self.hdl:
-            if len(h.buffer_ptrs) != self.world or h.signal_pad_size < 4 * (_SLOT0 + MAX_WORLD):
+            if len(h.buffer_ptrs) != self.world or h.signal_pad_size < 4 * (_SLOT0 + 2 * MAX_WORLD):
                 raise RuntimeError("unexpected symmetric memory geometry")
         self._in = [_lib.ptr_array(list(h.buffer_ptrs)) for h in self.hdl]
         self._sig = [_lib.ptr_array(list(h.signal_pad_ptrs)) for h in self.hdl]
+        # NVSwitch multicast mapping of the two buffers (0 when the fabric has none): in-switch two-shot sum
+        self._mc = [int(getattr(h, "multicast_ptr", 0) or 0) for h in self.hdl]
+        if os.environ.get("PSGD_PEER_MULTICAST", "1") != "1" or not all(self._mc):
+            self._mc = [0, 0]
+        self.multicast = bool(self._mc[0])
         self.epoch = [0, 0]
         for b in self.buf:
             b.zero_()
@@ -48,6 +53,11 @@ class PeerExchange:
         """out[:n] = sum over ranks of buf[which][:n]  (which: 0 = P || flat, 1 = Q)."""
         self.epoch[which] += 1
         stream = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
+        if self._mc[which]:
+            _lib.check(self._lib.psgd_peer_allreduce_mc(self._in[which], self._sig[which], ctypes.c_void_p(self._mc[which]),
+                                                        out.data_ptr(), n, self.rank, self.world, _SLOT0,
+                                                        self.epoch[which], self.device.index, stream), self._lib)
+            return
         _lib.check(self._lib.psgd_peer_allreduce(self._in[which], self._sig[which], out.data_ptr(), n, self.rank,
                                                  self.world, _SLOT0, self.epoch[which], self.device.index, stream),
                    self._lib)

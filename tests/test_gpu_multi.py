@@ -52,20 +52,25 @@ for name in ("w2_r2_reuse", "w2_r3_fresh"):
         for t, ref in zip(mem, unflatten(g.get(rank, step, "mem"), g.shapes, device=dev)):
             t.copy_(ref)
 dist.destroy_process_group()
-print("rank", rank, "ok", "peer=%s" % (red._peer is not None))
+print("rank", rank, "ok", "peer=%s" % (red._peer is not None),
+      "multicast=%s" % bool(red._peer is not None and red._peer.multicast))
 '''
 
 
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
-@pytest.mark.parametrize("peer", ["1", "0"])  # own peer-memory all-reduce kernel / torch.distributed (NCCL)
+# own all-reduce through the NVSwitch multicast mapping / own one-shot peer pull / torch.distributed (NCCL)
+@pytest.mark.parametrize("peer", ["multicast", "pull", "nccl"])
 def test_two_gpus_match_two_rank_reference(tmp_path, peer):
     script = tmp_path / "worker.py"
     script.write_text(WORKER)
-    env = dict(os.environ, PSGD_ROOT=ROOT, PSGD_PEER_ALLREDUCE=peer, PSGD_DEBUG="1")
+    env = dict(os.environ, PSGD_ROOT=ROOT, PSGD_PEER_ALLREDUCE="0" if peer == "nccl" else "1",
+               PSGD_PEER_MULTICAST="1" if peer == "multicast" else "0", PSGD_DEBUG="1")
     out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
                           "--master-addr", "127.0.0.1", "--master-port", "29533", str(script)],
-                         env=env, capture_output=True, text=True, timeout=600)
+                         env=env, capture_output=True, text=True, timeout=300)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
     assert out.stdout.count("ok") == 2
-    if peer == "1":
+    if peer != "nccl":
         assert "peer=True" in out.stdout, out.stdout[-2000:]
+    if peer == "multicast" and "multicast=True" not in out.stdout:
+        pytest.skip("no multicast mapping on this fabric: the pull kernel ran instead")
