@@ -1,13 +1,15 @@
 """Peer-memory exchange for the two packed all-reduces of a step (reducer.py:126,132,145) inside one NVLink domain.
 
 The input buffers of the two phases live in torch symmetric memory (every rank maps every other rank's buffer and
-signal pad); the sum itself is this package's own kernel (psgd_peer_allreduce): each rank reads all ranks' inputs
-and adds them in rank order, so every rank gets the same bits.  Set-up is a collective; if it fails on any rank
-every rank falls back to torch.distributed.all_reduce (NCCL).
+signal pad); the sum itself is this package's own kernel.  Where the fabric gives the buffers a multicast mapping
+(NVSwitch), psgd_peer_allreduce_mc sums rank k's slice inside the switch (multimem.ld_reduce) and stores it into every
+rank's copy (multimem.st); otherwise psgd_peer_allreduce has each rank read all ranks' inputs and add them in rank
+order.  Either way every rank gets the same bits.  Set-up is a collective; if it fails on any rank every rank falls
+back to torch.distributed.all_reduce (NCCL).
 
-Opt-in (PSGD_PEER_ALLREDUCE=1).  Measured on 8 x B200 (DistilBERT r=4 step): 2 GPUs 0.310 ms vs 0.315 ms with NCCL,
-4 GPUs 0.325 vs 0.324, 8 GPUs 0.356 vs 0.346 -- a one-shot pull reads (world-1) x the message, NCCL's in-switch
-reduction wins from 8 ranks on, so NCCL stays the default."""
+Opt-in (PSGD_PEER_ALLREDUCE=1; PSGD_PEER_MULTICAST=0 forces the pull kernel).  Measured on 8 x B200 (DistilBERT r=4
+step) for the pull kernel: 2 GPUs 0.310 ms vs 0.315 ms with NCCL, 4 GPUs 0.325 vs 0.324, 8 GPUs 0.356 vs 0.346 -- a
+one-shot pull reads (world-1) x the message, so NCCL stays the default; DESIGN.md section 6 has the multicast numbers."""
 import ctypes
 import os
 
