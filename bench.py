@@ -275,6 +275,9 @@ def run_b200(args):
     barrier()
     t_wall1 = time.time()
     launches = lib.psgd_launch_count() - launches0
+    px = getattr(red, "_peer", None)
+    allreduce_kind = ("none (1 GPU)" if world == 1 else "torch.distributed NCCL" if px is None else
+                      "own kernel, NVSwitch multicast (multimem)" if px.multicast else "own kernel, peer pull")
     ms = ev0.elapsed_time(ev1)
     phases = plan.timing_read() if not args.no_phase_timing else {}
     plan.timing_enable(False)
@@ -488,6 +491,7 @@ def run_b200(args):
         "ms_per_step": ms_per_step, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic", "config": workload_config(args, st),
         "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
+        "allreduce": allreduce_kind,
         "clocks": clocks, "phases": phase_report,
         "phases_note": "per-phase event brackets measured in a separate pass (they add ~13 % to the step and keep the kernels from overlapping head to tail); "
                        "inside the timed region only finalize is bracketed, on every 4th step",

@@ -7,9 +7,9 @@ rank's copy (multimem.st); otherwise psgd_peer_allreduce has each rank read all 
 order.  Either way every rank gets the same bits.  Set-up is a collective; if it fails on any rank every rank falls
 back to torch.distributed.all_reduce (NCCL).
 
-Opt-in (PSGD_PEER_ALLREDUCE=1; PSGD_PEER_MULTICAST=0 forces the pull kernel).  Measured on 8 x B200 (DistilBERT r=4
-step) for the pull kernel: 2 GPUs 0.310 ms vs 0.315 ms with NCCL, 4 GPUs 0.325 vs 0.324, 8 GPUs 0.356 vs 0.346 -- a
-one-shot pull reads (world-1) x the message, so NCCL stays the default; DESIGN.md section 6 has the multicast numbers."""
+PSGD_PEER_ALLREDUCE: 1 / 0 force it on / off; unset, the multicast kernel is used from 8 ranks on and NCCL below
+(PSGD_PEER_MULTICAST=0 forces the pull kernel where the exchange is on).  Measured DistilBERT r=4 step on B200s:
+2 GPUs NCCL 0.280 ms, pull 0.278, multicast 0.302; 8 GPUs NCCL 0.307, pull 0.318, multicast 0.294."""
 import ctypes
 import os
 
@@ -65,15 +65,30 @@ class PeerExchange:
                    self._lib)
 
 
+AUTO_MIN_WORLD = 8   # from this many ranks on the multicast kernel beat NCCL in the measurements
+
+
+def mode_for(world, setting):
+    """What PSGD_PEER_ALLREDUCE asks for: 'off', 'on' (either kernel) or 'multicast-only'.
+    '1' / '0' force it on / off; unset (or 'auto') turns the multicast kernel on from AUTO_MIN_WORLD ranks."""
+    if world < 2 or world > MAX_WORLD or setting == "0":
+        return "off"
+    if setting == "1":
+        return "on"
+    return "multicast-only" if world >= AUTO_MIN_WORLD else "off"
+
+
 def try_setup(device, n_pf, n_q):
     """Collective.  Returns a PeerExchange on every rank, or None on every rank."""
     world = dist.get_world_size()
-    if (world < 2 or world > MAX_WORLD or device.type != "cuda" or os.environ.get("PSGD_PEER_ALLREDUCE", "0") != "1"
-            or dist.get_backend() != "nccl"):
+    mode = mode_for(world, os.environ.get("PSGD_PEER_ALLREDUCE", "auto"))
+    if mode == "off" or device.type != "cuda" or dist.get_backend() != "nccl":
         return None
     ex, ok = None, 1
     try:
         ex = PeerExchange(device, n_pf, n_q)
+        if mode == "multicast-only" and not ex.multicast:
+            ok = 0  # the pull kernel loses to NCCL at this size
     except Exception as exc:  # noqa: BLE001 -- any failure means "use NCCL", decided jointly below
         ok = 0
         if os.environ.get("PSGD_DEBUG"):

@@ -145,3 +145,13 @@ def test_module_helpers():
     assert R.all_reduce(torch.zeros(1)) is None  # world 1: skipped (reducer.py:193-195)
     with pytest.raises(RuntimeError, match="no CPU fallback|CUDA"):
         R.orthogonalize(torch.randn(4, 2))
+
+
+def test_peer_allreduce_selection():
+    """PSGD_PEER_ALLREDUCE: forced on / off, otherwise the multicast kernel from 8 ranks on (peer.py)."""
+    from network_distributed_pytorch_b200 import peer
+
+    assert peer.mode_for(1, "auto") == "off" and peer.mode_for(2, "auto") == "off" and peer.mode_for(4, "auto") == "off"
+    assert peer.mode_for(8, "auto") == "multicast-only"
+    assert peer.mode_for(8, "0") == "off" and peer.mode_for(2, "1") == "on" and peer.mode_for(8, "1") == "on"
+    assert peer.mode_for(peer.MAX_WORLD + 1, "1") == "off"
