@@ -48,6 +48,12 @@ class PeerExchange:
         self.epoch = [0, 0]
         for b in self.buf:
             b.zero_()
+        # The flag slots must start below the first epoch.  Symmetric allocations are recycled, so a pad may still hold
+        # the epochs of an earlier exchange (a second reducer in the same process): every rank clears its own slots
+        # before anybody may signal.
+        for h in self.hdl:
+            pad = h.get_signal_pad(self.rank, (h.signal_pad_size // 4,), torch.int32)
+            pad[_SLOT0 : _SLOT0 + 2 * MAX_WORLD].zero_()
         torch.cuda.synchronize(device)
         dist.barrier()
 

@@ -21,7 +21,15 @@ rank = int(os.environ["RANK"]); local = int(os.environ["LOCAL_RANK"])
 torch.cuda.set_device(local); dev = torch.device("cuda", local)
 dist.init_process_group("nccl", device_id=dev)
 TOL = 1e-5
-for name in ("w2_r2_reuse", "w2_r3_fresh"):
+red = None
+for name in ("w2_r2_reuse", "w2_r3_fresh", "w2_r2_reuse"):
+    if red is not None:  # let go of the previous reducer, so that its symmetric buffers and signal pads get recycled
+        import gc
+        peer_seen = red._peer is not None
+        red._set_random = None
+        red = None
+        gc.collect()
+        torch.cuda.synchronize()
     g = Golden(name)
     red = PowerSGDReducer(g.seed, dev, 0, g.reuse, g.rank)
     assert red.n_workers == 2
