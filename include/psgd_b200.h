@@ -164,10 +164,12 @@ int psgd_peer_allreduce(const void* const* peer_in, void* const* peer_signal, fl
  * address of the buffer whose per-rank addresses are peer_in[]; torch: symmetric-memory handle .multicast_ptr):
  * rank k sums the k-th slice inside the switch (multimem.ld_reduce) and stores it into every rank's copy
  * (multimem.st), in place; `out[0 .. n)` then receives this rank's copy.  The symmetric buffers must be padded to a
- * multiple of 4 floats (the padding takes part in the sum).  Uses signal slots slot0 .. slot0 + 15.  Same
- * alternation rule as above. */
+ * multiple of 4 floats (the padding takes part in the sum).  out[i] = sum / out_div for i >= div_from, the plain sum
+ * below (the `/= n_workers` of reducer.py:147,167 on the way out; out_div = 1 leaves everything a sum).  Uses signal
+ * slots slot0 .. slot0 + 15.  Same alternation rule as above. */
 int psgd_peer_allreduce_mc(const void* const* peer_in, void* const* peer_signal, void* multicast, float* out, int64_t n,
-                           int rank, int world, int slot0, uint32_t epoch, int device, psgd_stream stream);
+                           int rank, int world, int slot0, uint32_t epoch, float out_div, int64_t div_from, int device,
+                           psgd_stream stream);
 
 /* In-place modified Gram-Schmidt of one n x r row-major matrix: the module-level
  * orthogonalize(matrix) of reducer.py:180-191. */

@@ -54,7 +54,7 @@ SIGNATURES = {
     "psgd_peer_allreduce": (ctypes.c_int, [vp, vp, vp, ctypes.c_int64, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                            ctypes.c_uint32, ctypes.c_int, vp]),
     "psgd_peer_allreduce_mc": (ctypes.c_int, [vp, vp, vp, vp, ctypes.c_int64, ctypes.c_int, ctypes.c_int, ctypes.c_int,
-                                              ctypes.c_uint32, ctypes.c_int, vp]),
+                                              ctypes.c_uint32, ctypes.c_float, ctypes.c_int64, ctypes.c_int, vp]),
     "psgd_orthogonalize_one": (ctypes.c_int, [vp, ctypes.c_int64, ctypes.c_int, ctypes.c_int, vp]),
     "psgd_q_from_mt_noalloc": (ctypes.c_int, [vp, vp, vp, ctypes.c_int64, ctypes.c_int64, ctypes.c_int, ctypes.c_int, vp]),
 }

@@ -1322,7 +1322,9 @@ int psgd_peer_allreduce(const void* const* peer_in, void* const* peer_signal, fl
 }
 
 int psgd_peer_allreduce_mc(const void* const* peer_in, void* const* peer_signal, void* multicast, float* out, int64_t n,
-                           int rank, int world, int slot0, uint32_t epoch, int device, psgd_stream stream) {
+                           int rank, int world, int slot0, uint32_t epoch, float out_div, int64_t div_from, int device,
+                           psgd_stream stream) {
+  if (!(out_div > 0.f) || div_from < 0) return fail("psgd_peer_allreduce_mc: out_div must be positive, div_from >= 0");
   if (world < 1 || world > kMaxPeers) return fail("psgd_peer_allreduce_mc: world size %d not in 1..%d", world, kMaxPeers);
   if (rank < 0 || rank >= world) return fail("psgd_peer_allreduce_mc: bad rank");
   if (n < 0 || !peer_in || !peer_signal || !multicast || (n && !out)) return fail("psgd_peer_allreduce_mc: bad argument");
@@ -1340,7 +1342,8 @@ int psgd_peer_allreduce_mc(const void* const* peer_in, void* const* peer_signal,
   const long long n4 = (n + 3) / 4;
   // every CTA takes part in both flag barriers, so the grid must be resident at once: at most one CTA per SM
   const unsigned grid = (unsigned)std::min<long long>(128, std::max<long long>(1, (n4 + kThreads - 1) / kThreads));
-  k_peer_allreduce_mc<<<grid, kThreads, 0, s>>>(a, (float*)multicast, out, (long long)n, rank, world, slot0, epoch);
+  k_peer_allreduce_mc<<<grid, kThreads, 0, s>>>(a, (float*)multicast, out, (long long)n, rank, world, slot0, epoch, out_div,
+                                                (long long)div_from);
   return check_launch("k_peer_allreduce_mc");
 }
 

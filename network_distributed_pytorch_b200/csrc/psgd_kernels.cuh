@@ -1071,7 +1071,7 @@ __device__ __forceinline__ void peer_flags_wait(const unsigned* flags, int world
 
 __global__ void __launch_bounds__(kThreads)
 k_peer_allreduce_mc(PeerArgs a, float* __restrict__ mc, float* __restrict__ out, long long n, int rank, int world,
-                    int slot0, unsigned epoch) {
+                    int slot0, unsigned epoch, float out_div, long long div_from) {
   __shared__ int s_last;
   const long long n4 = (n + 3) >> 2;  // the symmetric buffers are padded to whole float4s, `out` is not
   if (blockIdx.x == 0 && (int)threadIdx.x < world) {
@@ -1103,10 +1103,23 @@ k_peer_allreduce_mc(PeerArgs a, float* __restrict__ mc, float* __restrict__ out,
 
   const float* mine = a.in[rank];
   const long long full4 = n >> 2;
-  for (long long i = (long long)blockIdx.x * kThreads + threadIdx.x; i < full4; i += stride)
-    reinterpret_cast<float4*>(out)[i] = ld_sys4(mine + 4 * i);
-  for (long long i = (full4 << 2) + (long long)blockIdx.x * kThreads + threadIdx.x; i < n; i += stride)
-    out[i] = ld_sys1(mine + i);
+  // the mean of reducer.py:128,147,167 can be formed on the way out: elements from div_from on leave as sum / out_div
+  for (long long i = (long long)blockIdx.x * kThreads + threadIdx.x; i < full4; i += stride) {
+    float4 v = ld_sys4(mine + 4 * i);
+    if (out_div != 1.0f) {
+      const long long e = 4 * i;
+      if (e >= div_from) v.x = v.x / out_div;
+      if (e + 1 >= div_from) v.y = v.y / out_div;
+      if (e + 2 >= div_from) v.z = v.z / out_div;
+      if (e + 3 >= div_from) v.w = v.w / out_div;
+    }
+    reinterpret_cast<float4*>(out)[i] = v;
+  }
+  for (long long i = (full4 << 2) + (long long)blockIdx.x * kThreads + threadIdx.x; i < n; i += stride) {
+    float v = ld_sys1(mine + i);
+    if (out_div != 1.0f && i >= div_from) v = v / out_div;
+    out[i] = v;
+  }
 }
 
 }  // namespace psgd

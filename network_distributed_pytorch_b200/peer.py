@@ -57,14 +57,18 @@ class PeerExchange:
         torch.cuda.synchronize(device)
         dist.barrier()
 
-    def allreduce(self, which, out, n):
-        """out[:n] = sum over ranks of buf[which][:n]  (which: 0 = P || flat, 1 = Q)."""
+    def allreduce(self, which, out, n, div=1.0, div_from=0):
+        """out[:n] = sum over ranks of buf[which][:n]  (which: 0 = P || flat, 1 = Q).  With the multicast kernel the
+        elements from div_from on leave as sum / div (callers check .multicast before asking for that)."""
+        if div != 1.0 and not self._mc[which]:
+            raise RuntimeError("the pull kernel returns plain sums")
         self.epoch[which] += 1
         stream = ctypes.c_void_p(torch.cuda.current_stream(self.device).cuda_stream)
         if self._mc[which]:
             _lib.check(self._lib.psgd_peer_allreduce_mc(self._in[which], self._sig[which], ctypes.c_void_p(self._mc[which]),
                                                         out.data_ptr(), n, self.rank, self.world, _SLOT0,
-                                                        self.epoch[which], self.device.index, stream), self._lib)
+                                                        self.epoch[which], ctypes.c_float(div), div_from,
+                                                        self.device.index, stream), self._lib)
             return
         _lib.check(self._lib.psgd_peer_allreduce(self._in[which], self._sig[which], out.data_ptr(), n, self.rank,
                                                  self.world, _SLOT0, self.epoch[which], self.device.index, stream),

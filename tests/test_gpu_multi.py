@@ -59,6 +59,27 @@ for name in ("w2_r2_reuse", "w2_r3_fresh", "w2_r2_reuse"):
             assert torch.equal(both[0], both[1])
         for t, ref in zip(mem, unflatten(g.get(rank, step, "mem"), g.shapes, device=dev)):
             t.copy_(ref)
+# one extra power iteration (upstream asserts 0): the all-reduces run twice per step, the flat buffer travels once
+from oracle.powersgd_oracle import OracleReducer
+from tests.gpu_common import _last_q_init
+shapes = [(96, 64), (64,), (40, 200), (7,), (300, 3072), (5,)]
+gen = torch.Generator().manual_seed(5)
+ins = [[torch.randn(s, generator=gen) for s in shapes] for _ in range(2)]
+red._set_random = None
+red = PowerSGDReducer(714, dev, 0, True, 4, extra_power_iterations=1)
+gin = [t.to(dev) for t in ins[rank]]
+gout = [torch.zeros(s, device=dev) for s in shapes]
+mem = [torch.zeros(s, device=dev) for s in shapes]
+red.reduce(gin, gout, mem)
+torch.cuda.synchronize()
+orc = OracleReducer(714, "cpu", n_power_iterations=1, reuse_query=True, rank=4, n_workers=2)
+o_out = [[torch.zeros(s) for s in shapes] for _ in range(2)]
+o_mem = [[torch.zeros(s) for s in shapes] for _ in range(2)]
+orc.reduce(ins, o_out, o_mem, q_init=_last_q_init(red, shapes, 4, 0, 714))
+assert rel_err(red.p_memory.cpu().numpy(), orc.p_memory.numpy()) < TOL
+assert rel_err(red.q_memory.cpu().numpy(), orc.q_memory.numpy()) < TOL
+assert max(per_tensor_rel_err(flatten(gout), flatten(o_out[rank]), shapes)) < TOL
+assert max(per_tensor_mem_err(flatten(mem), flatten(o_mem[rank]), flatten(ins[rank]), shapes)) < TOL
 dist.destroy_process_group()
 print("rank", rank, "ok", "peer=%s" % (red._peer is not None),
       "multicast=%s" % bool(red._peer is not None and red._peer.multicast))
