@@ -34,7 +34,7 @@ typedef struct psgd_tb psgd_tb;
 typedef struct psgd_sgd psgd_sgd;
 typedef void* psgd_stream;
 
-#define PSGD_ABI_VERSION 1
+#define PSGD_ABI_VERSION 2
 #define PSGD_MAX_RANK 32
 
 /* phases, used by the tile and timing queries */
@@ -166,10 +166,12 @@ int psgd_peer_allreduce(const void* const* peer_in, void* const* peer_signal, fl
  * (multimem.st), in place; `out[0 .. n)` then receives this rank's copy.  The symmetric buffers must be padded to a
  * multiple of 4 floats (the padding takes part in the sum).  out[i] = sum / out_div for i >= div_from, the plain sum
  * below (the `/= n_workers` of reducer.py:147,167 on the way out; out_div = 1 leaves everything a sum).  Uses signal
- * slots slot0 .. slot0 + 15.  Same alternation rule as above. */
+ * slots slot0 .. slot0 + 15.  Same alternation rule as above.  blocks_done: one zero-initialised device word owned by
+ * this call site (the kernel counts its finished CTAs there and leaves it at zero); two call sites that may overlap
+ * on the GPU (different streams, different reducers) must not share one. */
 int psgd_peer_allreduce_mc(const void* const* peer_in, void* const* peer_signal, void* multicast, float* out, int64_t n,
-                           int rank, int world, int slot0, uint32_t epoch, float out_div, int64_t div_from, int device,
-                           psgd_stream stream);
+                           int rank, int world, int slot0, uint32_t epoch, float out_div, int64_t div_from,
+                           uint32_t* blocks_done, int device, psgd_stream stream);
 
 /* In-place modified Gram-Schmidt of one n x r row-major matrix: the module-level
  * orthogonalize(matrix) of reducer.py:180-191. */

@@ -12,6 +12,7 @@ c_vpp = ctypes.POINTER(ctypes.c_void_p)
 vp = ctypes.c_void_p
 
 N_PHASES = 7
+ABI_VERSION = 2  # PSGD_ABI_VERSION of include/psgd_b200.h
 PHASE_NAMES = ["pack", "p_from_m", "orthogonalize", "q_from_mt", "q_reduce", "finalize", "finish"]
 PHASE_PACK, PHASE_P_FROM_M, PHASE_ORTH, PHASE_Q_FROM_MT, PHASE_Q_REDUCE, PHASE_FINALIZE, PHASE_FINISH = range(7)
 
@@ -54,7 +55,7 @@ SIGNATURES = {
     "psgd_peer_allreduce": (ctypes.c_int, [vp, vp, vp, ctypes.c_int64, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                            ctypes.c_uint32, ctypes.c_int, vp]),
     "psgd_peer_allreduce_mc": (ctypes.c_int, [vp, vp, vp, vp, ctypes.c_int64, ctypes.c_int, ctypes.c_int, ctypes.c_int,
-                                              ctypes.c_uint32, ctypes.c_float, ctypes.c_int64, ctypes.c_int, vp]),
+                                              ctypes.c_uint32, ctypes.c_float, ctypes.c_int64, vp, ctypes.c_int, vp]),
     "psgd_orthogonalize_one": (ctypes.c_int, [vp, ctypes.c_int64, ctypes.c_int, ctypes.c_int, vp]),
     "psgd_q_from_mt_noalloc": (ctypes.c_int, [vp, vp, vp, ctypes.c_int64, ctypes.c_int64, ctypes.c_int, ctypes.c_int, vp]),
 }
@@ -81,7 +82,7 @@ def load():
         fn = getattr(lib, name)  # AttributeError here = header/library mismatch
         fn.restype = res
         fn.argtypes = args
-    if lib.psgd_abi_version() != 1:
+    if lib.psgd_abi_version() != ABI_VERSION:
         raise PsgdError("libpsgd_b200.so has an unexpected ABI version")
     _lib = lib
     return lib

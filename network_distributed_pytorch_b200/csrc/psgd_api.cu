@@ -6,6 +6,8 @@
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
+#include <map>
+#include <mutex>
 #include <string>
 #include <utility>
 #include <vector>
@@ -51,6 +53,7 @@ int pow2_ceil(long long x) {
 }
 
 constexpr int kSlots = 4;
+constexpr int kCtrRing = 8;
 
 struct Timer {
   cudaEvent_t a, b;
@@ -92,7 +95,13 @@ struct psgd_plan {
   int* d_direct_row_pre = nullptr;
   StreamTask* d_tasks1 = nullptr;
   StreamTask* d_tasks4 = nullptr;
-  int* d_counters = nullptr;  // [0..1] K1 task / done counters, [2..3] K4
+  // Task / done counter pairs of the streamed kernels.  A launch may start (programmatic dependent launch) while an
+  // earlier launch of the same kernel is still draining, and its producers take their first task before they wait
+  // for their predecessors, so consecutive launches must not share a pair: each launch takes the next pair of a
+  // ring of kCtrRing, K1 from [0, 2 kCtrRing), K4 from [2 kCtrRing, 4 kCtrRing).  The last CTA of a launch re-arms
+  // the pair it used.
+  int* d_counters = nullptr;
+  unsigned seq1 = 0, seq4 = 0;
   int n_ctr3 = 0;
   int* d_ctr3 = nullptr;  // K3: completion counter per (matrix, column tile), zero between launches
   unsigned long long* d_dbg = nullptr;  // PSGD_STREAM_DEBUG: per-CTA cycle breakdown of the last streamed K1
@@ -101,7 +110,6 @@ struct psgd_plan {
   int stream_grid = 148, ring_slot_bytes = 0, ring_slots = 0, q_bytes = 0;
   int ring_slot_bytes1 = 0, ring_slots1 = 0;  // K1's own ring geometry (same shared-memory budget)
   size_t stream_smem = 0;
-  bool attr1_set = false, attr1f_set = false, attr4_set = false;  // opt-in shared memory size set on the streamed kernels
   // device tables
   MatDesc* d_mats = nullptr;
   int4* d_tiles1 = nullptr;
@@ -282,10 +290,26 @@ int need_ptrs(const psgd_plan* p) {
   return 0;
 }
 
+// The opt-in dynamic shared-memory limit belongs to the kernel function (per device), not to a plan: several plans
+// with different stage sizes share one instantiation.  The limit is therefore only ever raised, process-wide.
+std::mutex g_attr_mu;
+std::map<std::pair<const void*, int>, int> g_attr_max;
+
+int raise_smem_limit(const void* f, size_t bytes) {
+  if (bytes <= 48 * 1024) return 0;
+  int device = 0;
+  CU(cudaGetDevice(&device));
+  std::lock_guard<std::mutex> lk(g_attr_mu);
+  int& cur = g_attr_max[std::make_pair(f, device)];
+  if ((int)bytes > cur) {
+    CU(cudaFuncSetAttribute(f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
+    cur = (int)bytes;
+  }
+  return 0;
+}
 template <typename F>
 int set_smem(F* f, size_t bytes) {
-  if (bytes > 48 * 1024) CU(cudaFuncSetAttribute((const void*)f, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes));
-  return 0;
+  return raise_smem_limit((const void*)f, bytes);
 }
 
 // Launch with the optional attributes of this library: thread-block cluster size and programmatic stream
@@ -569,8 +593,8 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
     rc |= upload(&p->d_qtiles, p->qtiles);
     rc |= upload(&p->d_tasks1, p->tasks1);
     rc |= upload(&p->d_tasks4, p->tasks4);
-    if (!rc && cudaMalloc((void**)&p->d_counters, 4 * sizeof(int)) != cudaSuccess) rc = fail("cudaMalloc(counters) failed");
-    if (!rc && cudaMemset(p->d_counters, 0, 4 * sizeof(int)) != cudaSuccess) rc = fail("cudaMemset(counters) failed");
+    if (!rc && cudaMalloc((void**)&p->d_counters, 4 * kCtrRing * sizeof(int)) != cudaSuccess) rc = fail("cudaMalloc(counters) failed");
+    if (!rc && cudaMemset(p->d_counters, 0, 4 * kCtrRing * sizeof(int)) != cudaSuccess) rc = fail("cudaMemset(counters) failed");
     if (!rc && p->n_ctr3) {
       if (cudaMalloc((void**)&p->d_ctr3, (size_t)p->n_ctr3 * sizeof(int)) != cudaSuccess ||
           cudaMemset(p->d_ctr3, 0, (size_t)p->n_ctr3 * sizeof(int)) != cudaSuccess) rc = fail("cudaMalloc(ctr3) failed");
@@ -862,17 +886,15 @@ static int p_from_m_impl(psgd_plan* p, float* p_mem, const float* q_mem, int fus
   const unsigned grid = (unsigned)p->tiles1.size();
   PhaseScope ts(p, PSGD_PHASE_P_FROM_M, s);
   if (fuse_add ? p->stream1f_now : p->stream1_now) {
-    StreamPlan sp{p->d_tasks1, p->d_counters, (int)p->tasks1.size(), p->ring_slot_bytes1, p->ring_slots1, p->q_bytes, p->d_dbg,
+    StreamPlan sp{p->d_tasks1, p->d_counters + 2 * (p->seq1++ % kCtrRing), (int)p->tasks1.size(), p->ring_slot_bytes1, p->ring_slots1, p->q_bytes, p->d_dbg,
                   p->d_vtiles, flat, fold ? (int)p->vtiles.size() : 0, fold ? (fuse_add ? 2 : 1) : 0, 1.0f,
                   p->d_direct_ids, p->d_direct_row_pre, (int)p->direct_ids.size(), p->split_max_sub};
     DISPATCH_R(p->R, {
       if (fuse_add) {
-        if (!p->attr1f_set) CU(cudaFuncSetAttribute((const void*)k_p_from_m_stream<RR, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->stream_smem));
-        p->attr1f_set = true;
+        if (set_smem(k_p_from_m_stream<RR, true>, p->stream_smem)) return 1;
         CU(launch_ex(k_p_from_m_stream<RR, true>, dim3(p->stream_grid), dim3(kStreamThreads), p->stream_smem, s, 1, p->pdl, dp, p->slot, sp, q_mem, p_mem, q_div));
       } else {
-        if (!p->attr1_set) CU(cudaFuncSetAttribute((const void*)k_p_from_m_stream<RR, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->stream_smem));
-        p->attr1_set = true;
+        if (set_smem(k_p_from_m_stream<RR, false>, p->stream_smem)) return 1;
         CU(launch_ex(k_p_from_m_stream<RR, false>, dim3(p->stream_grid), dim3(kStreamThreads), p->stream_smem, s, 1, p->pdl, dp, p->slot, sp, q_mem, p_mem, q_div));
       }
     });
@@ -1014,12 +1036,11 @@ static int finalize_impl(psgd_plan* p, const float* p_mem, const float* q_mem, f
   const unsigned grid = (unsigned)p->tiles4.size();
   PhaseScope ts(p, PSGD_PHASE_FINALIZE, s);
   if (p->stream4_now) {
-    StreamPlan sp{p->d_tasks4, p->d_counters + 2, (int)p->tasks4.size(), p->ring_slot_bytes, p->ring_slots, p->q_bytes, nullptr,
+    StreamPlan sp{p->d_tasks4, p->d_counters + 2 * kCtrRing + 2 * (p->seq4++ % kCtrRing), (int)p->tasks4.size(), p->ring_slot_bytes, p->ring_slots, p->q_bytes, nullptr,
                   p->d_vtiles, const_cast<float*>(flat), fold ? (int)p->vtiles.size() : 0, fold ? 3 : 0, n_workers,
                   p->d_direct_ids, p->d_direct_row_pre, (int)p->direct_ids.size(), 0};
     DISPATCH_R(p->R, {
-      if (!p->attr4_set) CU(cudaFuncSetAttribute((const void*)k_finalize_stream<RR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)p->stream_smem));
-      p->attr4_set = true;
+      if (set_smem(k_finalize_stream<RR>, p->stream_smem)) return 1;
       CU(launch_ex(k_finalize_stream<RR>, dim3(p->stream_grid), dim3(kStreamThreads), p->stream_smem, s, 1, p->pdl, dp, p->slot, sp, p_mem, q_mem, n_workers));
     });
     if (check_launch("k_finalize_stream")) return 1;
@@ -1322,8 +1343,9 @@ int psgd_peer_allreduce(const void* const* peer_in, void* const* peer_signal, fl
 }
 
 int psgd_peer_allreduce_mc(const void* const* peer_in, void* const* peer_signal, void* multicast, float* out, int64_t n,
-                           int rank, int world, int slot0, uint32_t epoch, float out_div, int64_t div_from, int device,
-                           psgd_stream stream) {
+                           int rank, int world, int slot0, uint32_t epoch, float out_div, int64_t div_from,
+                           uint32_t* blocks_done, int device, psgd_stream stream) {
+  if (!blocks_done) return fail("psgd_peer_allreduce_mc: blocks_done is null");
   if (!(out_div > 0.f) || div_from < 0) return fail("psgd_peer_allreduce_mc: out_div must be positive, div_from >= 0");
   if (world < 1 || world > kMaxPeers) return fail("psgd_peer_allreduce_mc: world size %d not in 1..%d", world, kMaxPeers);
   if (rank < 0 || rank >= world) return fail("psgd_peer_allreduce_mc: bad rank");
@@ -1343,7 +1365,7 @@ int psgd_peer_allreduce_mc(const void* const* peer_in, void* const* peer_signal,
   // every CTA takes part in both flag barriers, so the grid must be resident at once: at most one CTA per SM
   const unsigned grid = (unsigned)std::min<long long>(128, std::max<long long>(1, (n4 + kThreads - 1) / kThreads));
   k_peer_allreduce_mc<<<grid, kThreads, 0, s>>>(a, (float*)multicast, out, (long long)n, rank, world, slot0, epoch, out_div,
-                                                (long long)div_from);
+                                                (long long)div_from, blocks_done);
   return check_launch("k_peer_allreduce_mc");
 }
 

@@ -1040,8 +1040,8 @@ k_peer_allreduce(PeerArgs a, float* __restrict__ out, long long n, int rank, int
 // buffer: one multimem.ld_reduce returns the switch-side sum of all ranks' copies of an element, one multimem.st
 // writes it back into every rank's copy.  A second flag barrier ("every rank's slice is stored everywhere") and the
 // result is copied from this rank's copy to `out`.  Each element is summed exactly once, so all ranks hold the
-// same bits; a rank moves n/W elements over NVLink instead of (W-1) n.
-__device__ unsigned g_mc_blocks_done;
+// same bits; a rank moves n/W elements over NVLink instead of (W-1) n.  `blocks_done` is a zero-initialised word owned
+// by the call site (one per exchange buffer): the kernel leaves it at zero.
 
 __device__ __forceinline__ float4 mm_ld_reduce4(const float* mc) {
   float4 v;
@@ -1071,7 +1071,7 @@ __device__ __forceinline__ void peer_flags_wait(const unsigned* flags, int world
 
 __global__ void __launch_bounds__(kThreads)
 k_peer_allreduce_mc(PeerArgs a, float* __restrict__ mc, float* __restrict__ out, long long n, int rank, int world,
-                    int slot0, unsigned epoch, float out_div, long long div_from) {
+                    int slot0, unsigned epoch, float out_div, long long div_from, unsigned* __restrict__ blocks_done) {
   __shared__ int s_last;
   const long long n4 = (n + 3) >> 2;  // the symmetric buffers are padded to whole float4s, `out` is not
   if (blockIdx.x == 0 && (int)threadIdx.x < world) {
@@ -1090,10 +1090,10 @@ k_peer_allreduce_mc(PeerArgs a, float* __restrict__ mc, float* __restrict__ out,
   }
   __threadfence_system();
   __syncthreads();
-  if (threadIdx.x == 0) s_last = (atomicAdd(&g_mc_blocks_done, 1u) == gridDim.x - 1);
+  if (threadIdx.x == 0) s_last = (atomicAdd(blocks_done, 1u) == gridDim.x - 1);
   __syncthreads();
   if (s_last) {  // the whole slice of this rank is stored in every copy
-    if (threadIdx.x == 0) g_mc_blocks_done = 0;
+    if (threadIdx.x == 0) *blocks_done = 0;
     if ((int)threadIdx.x < world) {
       __threadfence_system();
       st_release_sys(a.sig[threadIdx.x] + slot0 + kMaxPeers + rank, epoch);

@@ -45,7 +45,9 @@ class PeerExchange:
         if os.environ.get("PSGD_PEER_MULTICAST", "1") != "1" or not all(self._mc):
             self._mc = [0, 0]
         self.multicast = bool(self._mc[0])
+        self.kind = "kernel-multicast" if self.multicast else "kernel-pull"
         self.epoch = [0, 0]
+        self._done = torch.zeros(2, dtype=torch.int32, device=device)  # per-buffer CTA completion word of the multicast kernel
         for b in self.buf:
             b.zero_()
         # The flag slots must start below the first epoch.  Symmetric allocations are recycled, so a pad may still hold
@@ -56,6 +58,10 @@ class PeerExchange:
             pad[_SLOT0 : _SLOT0 + 2 * MAX_WORLD].zero_()
         torch.cuda.synchronize(device)
         dist.barrier()
+
+    def describe(self):
+        return {"kernel-multicast": "own kernel, NVSwitch multicast (multimem), two-shot",
+                "kernel-pull": "own kernel, peer pull"}[self.kind]
 
     def allreduce(self, which, out, n, div=1.0, div_from=0):
         """out[:n] = sum over ranks of buf[which][:n]  (which: 0 = P || flat, 1 = Q).  With the multicast kernel the
@@ -68,7 +74,8 @@ class PeerExchange:
             _lib.check(self._lib.psgd_peer_allreduce_mc(self._in[which], self._sig[which], ctypes.c_void_p(self._mc[which]),
                                                         out.data_ptr(), n, self.rank, self.world, _SLOT0,
                                                         self.epoch[which], ctypes.c_float(div), div_from,
-                                                        self.device.index, stream), self._lib)
+                                                        self._done.data_ptr() + 4 * which, self.device.index, stream),
+                       self._lib)
             return
         _lib.check(self._lib.psgd_peer_allreduce(self._in[which], self._sig[which], out.data_ptr(), n, self.rank,
                                                  self.world, _SLOT0, self.epoch[which], self.device.index, stream),

@@ -144,11 +144,12 @@ class PowerSGDReducer(Reducer):
         world = self.n_workers
         bits_communicated = 0
 
-        # Host fast path: the very same storages as in the previous call (persistent send / grad / memory buffers)
-        # need no re-validation, no list splitting and no pointer upload.  The previous call's tensors are kept
-        # alive in the cache, so an equal address means the same storage, not a recycled one.
+        # Host fast path: a call whose tensors sit at the same addresses with the same shapes as in the previous call
+        # (persistent send / grad / memory buffers, or .grad tensors the caching allocator handed back in place)
+        # needs no re-validation, no list splitting and no pointer upload: the device-side pointer table is already
+        # right.  Only addresses and shapes are remembered, never the tensors, so nothing of the caller's is kept alive.
         sig = (fused, tuple([t.data_ptr() for t in grad_in]), tuple([t.data_ptr() for t in grad_out]),
-               tuple([t.data_ptr() for t in memory_out]))
+               tuple([t.data_ptr() for t in memory_out]), tuple([t.shape for t in grad_in]))
         cache = self._call_cache
         if cache is not None and cache[0] == sig and self.reuse_query:
             plan = cache[1]
@@ -197,7 +198,7 @@ class PowerSGDReducer(Reducer):
             else:
                 plan.set_ptrs(mats, [grad_out[i] for i in mat_idx], [memory_out[i] for i in mat_idx],
                               vecs, [grad_out[i] for i in vec_idx])
-            self._call_cache = (sig, plan, list(grad_in), list(grad_out), list(memory_out))
+            self._call_cache = (sig, plan)
         flat = self._flat
         px = self._peer
         if px is not None:  # phase inputs live in symmetric memory, results land in p_memory || flat and q_memory

@@ -36,7 +36,8 @@ def within_tolerance(res, tol=TOL):
     return bad
 
 
-def run_pair(shapes, rank, steps=1, reuse=True, seed=714, data_seed=0, extra=0, offset_elems=0, scale_cols=False):
+def run_pair(shapes, rank, steps=1, reuse=True, seed=714, data_seed=0, extra=0, offset_elems=0, scale_cols=False,
+             arbiter=True):
     """Run the CUDA reducer and the CPU oracle on the same seeded inputs and the same query.
 
     Returns a list (per step) of dicts with per-tensor relative errors of grad_out / memory_out and the
@@ -58,7 +59,8 @@ def run_pair(shapes, rank, steps=1, reuse=True, seed=714, data_seed=0, extra=0, 
 
     red = PowerSGDReducer(seed, dev, 0, reuse, rank, extra_power_iterations=extra)
     orc = OracleReducer(seed, "cpu", n_power_iterations=extra, reuse_query=reuse, rank=rank)
-    orc64 = OracleReducer(seed, "cpu", n_power_iterations=extra, reuse_query=reuse, rank=rank, dtype=torch.float64)
+    orc64 = (OracleReducer(seed, "cpu", n_power_iterations=extra, reuse_query=reuse, rank=rank, dtype=torch.float64)
+             if arbiter else None)
     mem_c = [torch.zeros(s) for s in shapes]
     mem_g = [on_gpu(t) for t in mem_c]
     results = []
@@ -77,10 +79,20 @@ def run_pair(shapes, rank, steps=1, reuse=True, seed=714, data_seed=0, extra=0, 
         q_init = None
         if drew:
             q_init = _last_q_init(red, shapes, rank, step, seed)
-        mem_prev = [t.double() for t in mem_c]
+        mem_prev = [t.double() for t in mem_c] if arbiter else None
         q_prev = orc.q_memory.clone() if orc.q_memory is not None else None
         bits_c = orc.reduce(send_c, out_c, mem_c, q_init=q_init)
         assert bits_g == bits_c
+        if not arbiter:  # large sets: fp32 oracle only
+            results.append(dict(
+                out=per_tensor_rel_err(flatten(out_g), flatten(out_c), shapes),
+                mem=per_tensor_mem_err(flatten(mem_g), flatten(mem_c), flatten(send_c), shapes),
+                p=per_tensor_rel_err(red.p_memory.cpu().numpy(), orc.p_memory.numpy(), [(red.p_memory.nelement(),)])[0],
+                q=per_tensor_rel_err(red.q_memory.cpu().numpy(), orc.q_memory.numpy(), [(red.q_memory.nelement(),)])[0],
+                send_equal=all(torch.equal(a.cpu(), b) for a, b in zip(send_g, send_c))))
+            for a, b in zip(mem_g, mem_c):
+                a.copy_(b)
+            continue
         # fp64 arbiter, single step from the same state as the fp32 runs
         out_d = [torch.zeros(s, dtype=torch.float64) for s in shapes]
         if q_init is None and q_prev is not None:

@@ -32,7 +32,7 @@ def test_every_declared_symbol_is_exported_and_bound(lib):
     for n in names:
         assert hasattr(lib, n), f"{n} declared in psgd_b200.h but not exported"
     assert set(names) == set(_lib.SIGNATURES), "ctypes table and header disagree"
-    assert lib.psgd_abi_version() == 1
+    assert lib.psgd_abi_version() == _lib.ABI_VERSION
 
 
 def test_compute_entry_points_fail_loudly_on_host_only_plan(lib):
@@ -50,16 +50,19 @@ def test_compute_entry_points_fail_loudly_on_host_only_plan(lib):
 def test_peer_allreduce_entry_points_validate_before_touching_the_gpu(lib):
     one = _lib.ptr_array([16])
     for fn, extra, tail in ((lib.psgd_peer_allreduce, (), ()),
-                            (lib.psgd_peer_allreduce_mc, (ctypes.c_void_p(16),), (ctypes.c_float(1.0), 0))):
+                            (lib.psgd_peer_allreduce_mc, (ctypes.c_void_p(16),), (ctypes.c_float(1.0), 0, ctypes.c_void_p(16)))):
         args = lambda world, rank, n=8, out=16: ((one, one) + extra + (ctypes.c_void_p(out), n, rank, world, 256, 1) + tail
                                                  + (0, None))
         assert fn(*args(9, 0)) != 0 and b"world size" in lib.psgd_last_error()
         assert fn(*args(1, 1)) != 0 and b"rank" in lib.psgd_last_error()
         assert fn(*args(1, 0, n=-1)) != 0
         assert fn(*args(1, 0, n=0)) == 0  # nothing to do, nothing launched
-    assert lib.psgd_peer_allreduce_mc(one, one, None, ctypes.c_void_p(16), 8, 0, 1, 256, 1, ctypes.c_float(1.0), 0, 0, None) != 0
+    assert lib.psgd_peer_allreduce_mc(one, one, None, ctypes.c_void_p(16), 8, 0, 1, 256, 1, ctypes.c_float(1.0), 0,
+                                      ctypes.c_void_p(16), 0, None) != 0
     assert lib.psgd_peer_allreduce_mc(one, one, ctypes.c_void_p(16), ctypes.c_void_p(16), 8, 0, 1, 256, 1,
-                                      ctypes.c_float(0.0), 0, 0, None) != 0 and b"out_div" in lib.psgd_last_error()
+                                      ctypes.c_float(0.0), 0, ctypes.c_void_p(16), 0, None) != 0 and b"out_div" in lib.psgd_last_error()
+    assert lib.psgd_peer_allreduce_mc(one, one, ctypes.c_void_p(16), ctypes.c_void_p(16), 8, 0, 1, 256, 1,
+                                      ctypes.c_float(1.0), 0, None, 0, None) != 0 and b"blocks_done" in lib.psgd_last_error()
 
 
 def split(shapes):
