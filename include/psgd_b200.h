@@ -102,6 +102,11 @@ int psgd_p_from_m(psgd_plan* plan, float* p_mem, const float* q_mem, int fuse_ad
  * one kernel and one launch gap less per step.  Falls back to two launches when the streamed kernel is not in use. */
 int psgd_p_from_m_pack(psgd_plan* plan, float* p_mem, const float* q_mem, int fuse_add, float q_div,
                        float* flat, psgd_stream stream);
+/* Single-worker convenience: psgd_p_from_m_pack (flat may be NULL: no gather) followed by
+ * psgd_orthogonalize(n_workers = 1) as ONE call, for the case where no all-reduce sits between reducer.py:121-123 and
+ * :136-137 (one worker).  Results are identical to the two separate calls. */
+int psgd_p_from_m_orth(psgd_plan* plan, float* p_mem, const float* q_mem, int fuse_add, float q_div,
+                       float* flat, psgd_stream stream);
 /* K2: p_mem /= n_workers then modified Gram-Schmidt of every P_i in place
  * (reducer.py:128, 136-137, 180-191). */
 int psgd_orthogonalize(psgd_plan* plan, float* p_mem, float n_workers, psgd_stream stream);
@@ -172,6 +177,42 @@ int psgd_peer_allreduce(const void* const* peer_in, void* const* peer_signal, fl
 int psgd_peer_allreduce_mc(const void* const* peer_in, void* const* peer_signal, void* multicast, float* out, int64_t n,
                            int rank, int world, int slot0, uint32_t epoch, float out_div, int64_t div_from,
                            uint32_t* blocks_done, int device, psgd_stream stream);
+
+/* ---- all-reduces taken into the kernels -------------------------------------------------------------
+ * Upstream runs dist.all_reduce on p_memory, on the flat <=1-D buffer and on q_memory (reducer.py:126, 132, 145), each
+ * followed by `/= n_workers`.  Inside one NVLink domain those three collectives need no launch of their own: the
+ * kernels that consume the sums read them "summed over all ranks" straight from symmetric memory.
+ *
+ * psgd_peer describes the two exchange buffers of a reducer as mapped into THIS process (e.g. torch symmetric memory):
+ *   pf_bufs[r] / q_bufs[r]  rank r's  P || flat  buffer (sum n*r + vec elements) and Q buffer (sum m*r elements), each
+ *                           padded to a multiple of 4 floats and 16-byte aligned; every rank writes its own copy
+ *                           (psgd_p_from_m* into pf_bufs[rank], psgd_q_from_mt into q_bufs[rank]);
+ *   pf_signals[r] / q_signals[r]  rank r's uint32 signal pad of that buffer; slots slot0 .. slot0 + world - 1 are used;
+ *   pf_multicast / q_multicast    NVSwitch multicast address of the buffer (mode 1), else NULL;
+ *   mode 1: one multimem.ld_reduce per element (the switch adds the ranks' copies); mode 2: one load per rank, added in
+ *           rank order (bit-identical on all ranks by construction, no multicast mapping needed).
+ * Every rank must issue the same sequence of *_peer calls (the handle counts barrier epochs).  Peer memory is read with
+ * plain and multimem loads only.  A crashed peer makes the waiting kernel trap after ~10 s instead of hanging. */
+typedef struct psgd_peer psgd_peer;
+int psgd_peer_create(int world, int rank, int device, const void* const* pf_bufs, void* const* pf_signals,
+                     const void* pf_multicast, const void* const* q_bufs, void* const* q_signals,
+                     const void* q_multicast, int slot0, int mode, psgd_peer** out);
+int psgd_peer_destroy(psgd_peer* peer);
+/* reducer.py:126-128 + 136-137 (+ 131-133, 167 for the flat buffer) as ONE launch: a flag barrier ("every rank's P is
+ * written"), then each Gram-Schmidt CTA loads its rows summed over the ranks, scales by 1 / n_workers, orthogonalises
+ * and stores P_hat to the local p_mem; spare CTAs leave mean(flat) in flat_out (NULL: the flat part is not touched,
+ * e.g. later power iterations).  Matrices too tall for the register-resident kernels fall back to a stand-alone
+ * reduction into p_mem followed by psgd_orthogonalize. */
+int psgd_orthogonalize_peer(psgd_plan* plan, psgd_peer* peer, float* p_mem, float* flat_out, psgd_stream stream);
+/* reducer.py:145-147 + 158-163 (+ 168) as ONE launch: the streamed finalize kernel first takes the flag barrier ("every
+ * rank's Q is written"), its CTAs sum one slice of Q each over the ranks, divide by n_workers and store the mean to the
+ * local q_mem, a grid-wide arrival count follows, then the kernel runs as at one worker.  flat: the averaged flat
+ * buffer psgd_orthogonalize_peer produced (scattered to vec_out as is). */
+int psgd_finalize_peer(psgd_plan* plan, psgd_peer* peer, const float* p_mem, float* q_mem, const float* flat,
+                       psgd_stream stream);
+/* K1 of a later power iteration at N > 1: the same Q prologue, then P = M mean(Q) into p_mem (this rank's part of
+ * pf_bufs).  q_mem: local buffer receiving mean(Q). */
+int psgd_p_from_m_peer(psgd_plan* plan, psgd_peer* peer, float* p_mem, float* q_mem, int fuse_add, psgd_stream stream);
 
 /* In-place modified Gram-Schmidt of one n x r row-major matrix: the module-level
  * orthogonalize(matrix) of reducer.py:180-191. */

@@ -36,6 +36,7 @@ SIGNATURES = {
     "psgd_pack_vec_fused": (ctypes.c_int, [vp, vp, vp]),
     "psgd_p_from_m": (ctypes.c_int, [vp, vp, vp, ctypes.c_int, ctypes.c_float, vp]),
     "psgd_p_from_m_pack": (ctypes.c_int, [vp, vp, vp, ctypes.c_int, ctypes.c_float, vp, vp]),
+    "psgd_p_from_m_orth": (ctypes.c_int, [vp, vp, vp, ctypes.c_int, ctypes.c_float, vp, vp]),
     "psgd_finalize_unpack": (ctypes.c_int, [vp, vp, vp, ctypes.c_float, vp, vp]),
     "psgd_orthogonalize": (ctypes.c_int, [vp, vp, ctypes.c_float, vp]),
     "psgd_q_from_mt": (ctypes.c_int, [vp, vp, vp, vp, vp]),
@@ -56,6 +57,12 @@ SIGNATURES = {
                                            ctypes.c_uint32, ctypes.c_int, vp]),
     "psgd_peer_allreduce_mc": (ctypes.c_int, [vp, vp, vp, vp, ctypes.c_int64, ctypes.c_int, ctypes.c_int, ctypes.c_int,
                                               ctypes.c_uint32, ctypes.c_float, ctypes.c_int64, vp, ctypes.c_int, vp]),
+    "psgd_peer_create": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, vp, vp, vp, vp, vp, vp, ctypes.c_int,
+                                        ctypes.c_int, ctypes.POINTER(vp)]),
+    "psgd_peer_destroy": (ctypes.c_int, [vp]),
+    "psgd_orthogonalize_peer": (ctypes.c_int, [vp, vp, vp, vp, vp]),
+    "psgd_finalize_peer": (ctypes.c_int, [vp, vp, vp, vp, vp, vp]),
+    "psgd_p_from_m_peer": (ctypes.c_int, [vp, vp, vp, vp, ctypes.c_int, vp]),
     "psgd_orthogonalize_one": (ctypes.c_int, [vp, ctypes.c_int64, ctypes.c_int, ctypes.c_int, vp]),
     "psgd_q_from_mt_noalloc": (ctypes.c_int, [vp, vp, vp, ctypes.c_int64, ctypes.c_int64, ctypes.c_int, ctypes.c_int, vp]),
 }

@@ -15,6 +15,7 @@
 #include "../../include/psgd_b200.h"
 #include "psgd_kernels.cuh"
 #include "psgd_stream.cuh"
+#include "psgd_tc.cuh"
 
 using namespace psgd;
 
@@ -107,9 +108,19 @@ struct psgd_plan {
   unsigned long long* d_dbg = nullptr;  // PSGD_STREAM_DEBUG: per-CTA cycle breakdown of the last streamed K1
   int4* d_tiles1_fb = nullptr;
   int4* d_tiles4_fb = nullptr;
+  int sm_count = 148;
   int stream_grid = 148, ring_slot_bytes = 0, ring_slots = 0, q_bytes = 0;
   int ring_slot_bytes1 = 0, ring_slots1 = 0;  // K1's own ring geometry (same shared-memory budget)
   size_t stream_smem = 0;
+  // tensor-pipe (3 x TF32) kernels for R >= 16: their own, larger row tiles over the matrices with m % 4 == 0; the
+  // rest stays with the FFMA direct kernels
+  bool tc = false;
+  int tc_mask = 0;  // PSGD_TC bits: 1 = K1, 2 = K3, 4 = K4
+  bool tc_now = false, tcf_now = false;  // per step: every such matrix (and its outputs / fused operands) is 16-byte aligned
+  int tc_wc1 = 0, tc_wc4 = 0;            // column chunk widths of the staged Q
+  size_t tc_smem1 = 0, tc_smem4 = 0;
+  std::vector<int4> tiles1_tc, tiles4_tc, tiles1_ntc, tiles4_ntc;
+  int4 *d_tiles1_tc = nullptr, *d_tiles4_tc = nullptr, *d_tiles1_ntc = nullptr, *d_tiles4_ntc = nullptr;
   // device tables
   MatDesc* d_mats = nullptr;
   int4* d_tiles1 = nullptr;
@@ -147,6 +158,14 @@ struct psgd_tb {
   cudaEvent_t slot_ev[kSlots] = {};
   bool slot_used[kSlots] = {};
   int cur = 0;
+};
+
+struct psgd_peer {
+  int device = -1, world = 1, rank = 0, mode = kPeerPull;
+  PeerLoad pf{}, q{};          // templates: P || flat buffer, Q buffer
+  unsigned epoch_pf = 0, epoch_q = 0;
+  unsigned* d_gsync = nullptr;  // grid-wide arrival counter of the Q prologue (monotonic)
+  unsigned gseq = 0;
 };
 
 namespace {
@@ -432,7 +451,8 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
     wo += (long long)md.nblk3 * md.m * md.r;
     wo = (wo + 3) & ~3LL;
     const int RL = kThreads3 / cgw;
-    const size_t s3 = ((size_t)md.t3_rows * R + (size_t)RL * md.cpt * R * (cgw + 1)) * 4;
+    size_t s3 = ((size_t)md.t3_rows * R + (size_t)RL * md.cpt * R * (cgw + 1)) * 4;
+    if (R >= 16) s3 = std::max(s3, (size_t)((md.t3_rows + 7) & ~7) * (R == 16 ? 24 : 40) * 4);  // tensor-pipe tile: P rows, padded pitch
     smem3 = std::max(smem3, s3);
     const int ncol = (int)((groups + cgw - 1) / cgw);
     if (md.n && md.m) {
@@ -479,6 +499,28 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
   };
   build_row_tiles(p, p->tiles1, t1_bytes, rows1, chunked_sets_for(rows1));
   build_row_tiles(p, p->tiles4, t4_bytes, rows4, chunked_sets_for(rows4));
+  // off by default: measured slower than the FFMA kernels in all three phases (tensor-pipe evaluation);
+  // PSGD_TC = 1 | 2 | 4 switches K1 | K3 | K4 to the tensor pipe
+  if (R >= 16 && env_ll("PSGD_TC", 0) != 0) {
+    p->tc = true;
+    p->tc_mask = (int)env_ll("PSGD_TC", 0);
+    p->tc_wc1 = R == 16 ? 768 : 384;
+    p->tc_wc4 = R == 16 ? 768 : 384;
+    const int wc1 = std::min(std::max((mmax + 15) & ~15, 16), p->tc_wc1);
+    p->tc_smem1 = (size_t)2 * R * tc_q_pitch(wc1) * 4;
+    p->tc_smem4 = (size_t)2 * p->tc_wc4 * (R + 1) * 4;
+    const long long tc_bytes = env_ll("PSGD_TC_TILE_BYTES", 384 * 1024);
+    std::vector<int4> all1, all4;
+    const int save_cap = p->wc_cap;
+    p->wc_cap = 1 << 30;  // no "chunked sets" floor for these tiles
+    build_row_tiles(p, all1, tc_bytes, 2, 1);  // granularity: 16 rows per warp pass
+    build_row_tiles(p, all4, tc_bytes, 2, 1);
+    p->wc_cap = save_cap;
+    for (const int4& t : all1) if (p->mats[t.x].m % 4 == 0) p->tiles1_tc.push_back(t);
+    for (const int4& t : all4) if (p->mats[t.x].m % 4 == 0) p->tiles4_tc.push_back(t);
+    for (const int4& t : p->tiles1) if (p->mats[t.x].m % 4 != 0) p->tiles1_ntc.push_back(t);
+    for (const int4& t : p->tiles4) if (p->mats[t.x].m % 4 != 0) p->tiles4_ntc.push_back(t);
+  }
 
   {  // streamed path: which matrices qualify, and the shared-memory split between Q stage and ring
     int smem_optin = 232448, sms = 148;
@@ -486,6 +528,7 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
       cudaDeviceGetAttribute(&smem_optin, cudaDevAttrMaxSharedMemoryPerBlockOptin, device);
       cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
     }
+    p->sm_count = sms;
     p->stream_grid = (int)env_ll("PSGD_STREAM_GRID", sms);
     const long long q_cap = env_ll("PSGD_STREAM_QCAP", 100 * 1024);
     long long slot = env_ll("PSGD_SLOT_BYTES", 48 * 1024);
@@ -607,9 +650,14 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
     rc |= upload(&p->d_direct_row_pre, p->direct_row_pre);
     rc |= upload(&p->d_tiles1_fb, p->tiles1_fb);
     rc |= upload(&p->d_tiles4_fb, p->tiles4_fb);
+    rc |= upload(&p->d_tiles1_tc, p->tiles1_tc);
+    rc |= upload(&p->d_tiles4_tc, p->tiles4_tc);
+    rc |= upload(&p->d_tiles1_ntc, p->tiles1_ntc);
+    rc |= upload(&p->d_tiles4_ntc, p->tiles4_ntc);
     rc |= upload(&p->d_orth_small, p->orth_small);
     rc |= upload(&p->d_orth_tall, p->orth_tall);
     rc |= upload(&p->d_orth_generic, p->orth_generic);
+
     // ring slot: 5 pointer arrays + flags per matrix, 2 pointer arrays per vector
     size_t sb = (size_t)n_mat * (5 * sizeof(void*) + sizeof(unsigned)) + (size_t)n_vec * 4 * sizeof(void*);
     sb = (sb + 255) & ~(size_t)255;
@@ -649,6 +697,10 @@ int psgd_plan_destroy(psgd_plan* p) {
     cudaFree(p->d_direct_row_pre);
     cudaFree(p->d_tiles1_fb);
     cudaFree(p->d_tiles4_fb);
+    cudaFree(p->d_tiles1_tc);
+    cudaFree(p->d_tiles4_tc);
+    cudaFree(p->d_tiles1_ntc);
+    cudaFree(p->d_tiles4_ntc);
     cudaFree(p->d_orth_small);
     cudaFree(p->d_orth_tall);
     cudaFree(p->d_orth_generic);
@@ -731,6 +783,7 @@ static int set_ptrs_impl(psgd_plan* p, const void* const* mat_in, void* const* m
   p->have_ge = grad && err;
   p->have_vge = vec_grad && vec_err;
   bool s1 = p->stream_ok, s4 = p->stream_ok, s1f = p->stream_ok && grad && err;
+  bool tc_all = p->tc, tcf_all = p->tc && grad && err;
   for (size_t i = 0; i < L; ++i) {
     const MatDesc& md = p->mats[i];
     const bool nonempty = md.n && md.m;
@@ -748,12 +801,18 @@ static int set_ptrs_impl(psgd_plan* p, const void* const* mat_in, void* const* m
     if (m4 && (((uintptr_t)mat_out[i] | (uintptr_t)mat_mem[i]) & 15) == 0) fl |= kFlagOutVec;
     if (p->have_ge && m4 && (((uintptr_t)grad[i] | (uintptr_t)err[i]) & 15) == 0) fl |= kFlagGeVec;
     h_fl[i] = fl;
+    if (p->tc && m4 && nonempty) {
+      if (!(fl & kFlagInVec) || !(fl & kFlagOutVec)) tc_all = false;
+      if (!(fl & kFlagInVec) || !(fl & kFlagOutVec) || !(fl & kFlagGeVec)) tcf_all = false;
+    }
     if (p->stream_ok && p->eligible[i]) {
       if (!(fl & kFlagInVec)) s1 = false;
       if (!(fl & kFlagInVec) || !(fl & kFlagGeVec)) s1f = false;
       if (!(fl & kFlagInVec) || !(fl & kFlagOutVec)) s4 = false;
     }
   }
+  p->tc_now = tc_all;
+  p->tcf_now = tcf_all;
   p->stream1_now = s1;
   p->stream1f_now = s1f;
   p->stream4_now = s4;
@@ -855,10 +914,22 @@ int psgd_pack_vec(psgd_plan* p, float* flat, psgd_stream stream) {
   }
 
 static int p_from_m_impl(psgd_plan* p, float* p_mem, const float* q_mem, int fuse_add, float q_div, float* flat,
-                         psgd_stream stream);
+                         psgd_stream stream, psgd_peer* peer = nullptr);
+static PeerQ peer_q_args(psgd_plan* p, psgd_peer* peer, float* q_mem);
+static int peer_reduce_standalone(psgd_peer* peer, int which, float* out, long long n, float div, long long div_from,
+                                  cudaStream_t s);
+static int orth_impl(psgd_plan* p, float* p_mem, float n_workers, psgd_stream stream);
 
 int psgd_p_from_m(psgd_plan* p, float* p_mem, const float* q_mem, int fuse_add, float q_div, psgd_stream stream) {
   return p_from_m_impl(p, p_mem, q_mem, fuse_add, q_div, nullptr, stream);
+}
+
+int psgd_p_from_m_orth(psgd_plan* p, float* p_mem, const float* q_mem, int fuse_add, float q_div, float* flat,
+                       psgd_stream stream) {
+  if (need_device(p) || need_ptrs(p)) return 1;
+  if (fuse_add && flat && !p->have_vge) return fail("psgd_p_from_m_orth: fuse_add needs psgd_set_ptrs_fused");
+  if (p_from_m_impl(p, p_mem, q_mem, fuse_add, q_div, flat, stream)) return 1;
+  return orth_impl(p, p_mem, 1.0f, stream);
 }
 
 int psgd_p_from_m_pack(psgd_plan* p, float* p_mem, const float* q_mem, int fuse_add, float q_div, float* flat,
@@ -870,9 +941,10 @@ int psgd_p_from_m_pack(psgd_plan* p, float* p_mem, const float* q_mem, int fuse_
 }
 
 static int p_from_m_impl(psgd_plan* p, float* p_mem, const float* q_mem, int fuse_add, float q_div, float* flat,
-                         psgd_stream stream) {
+                         psgd_stream stream, psgd_peer* peer) {
   if (need_device(p) || need_ptrs(p)) return 1;
-  const bool fold = flat && p->v_total && !p->tiles1.empty() && (fuse_add ? p->stream1f_now : p->stream1_now);
+  const bool tc1 = p->tc && (p->tc_mask & 1) && (fuse_add ? p->tcf_now : p->tc_now);
+  const bool fold = flat && p->v_total && !p->tiles1.empty() && !tc1 && (fuse_add ? p->stream1f_now : p->stream1_now);
   if (flat && p->v_total && !fold) {  // no streamed launch to ride on: separate gather
     if (fuse_add ? psgd_pack_vec_fused(p, flat, stream) : psgd_pack_vec(p, flat, stream)) return 1;
   }
@@ -885,17 +957,64 @@ static int p_from_m_impl(psgd_plan* p, float* p_mem, const float* q_mem, int fus
   const DevPlan dp = dev_plan(p);
   const unsigned grid = (unsigned)p->tiles1.size();
   PhaseScope ts(p, PSGD_PHASE_P_FROM_M, s);
+  if (tc1) {  // ranks 16 / 32: tensor pipe (3 x TF32), see psgd_tc.cuh
+    if (peer && peer_reduce_standalone(peer, 1, const_cast<float*>(q_mem), p->q_total, (float)peer->world, 0, s)) return 1;
+    if (!p->tiles1_tc.empty()) {
+      DevPlan tp = dp;
+      tp.tiles1 = p->d_tiles1_tc;
+      const unsigned g = (unsigned)p->tiles1_tc.size();
+      if (p->R == 16) {
+        if (fuse_add) {
+          if (set_smem(k_p_from_m_tc<16, true>, p->tc_smem1)) return 1;
+          k_p_from_m_tc<16, true><<<g, kTcThreads, p->tc_smem1, s>>>(tp, p->slot, q_mem, p_mem, q_div, p->tc_wc1);
+        } else {
+          if (set_smem(k_p_from_m_tc<16, false>, p->tc_smem1)) return 1;
+          k_p_from_m_tc<16, false><<<g, kTcThreads, p->tc_smem1, s>>>(tp, p->slot, q_mem, p_mem, q_div, p->tc_wc1);
+        }
+      } else {
+        if (fuse_add) {
+          if (set_smem(k_p_from_m_tc<32, true>, p->tc_smem1)) return 1;
+          k_p_from_m_tc<32, true><<<g, kTcThreads, p->tc_smem1, s>>>(tp, p->slot, q_mem, p_mem, q_div, p->tc_wc1);
+        } else {
+          if (set_smem(k_p_from_m_tc<32, false>, p->tc_smem1)) return 1;
+          k_p_from_m_tc<32, false><<<g, kTcThreads, p->tc_smem1, s>>>(tp, p->slot, q_mem, p_mem, q_div, p->tc_wc1);
+        }
+      }
+      if (check_launch("k_p_from_m_tc")) return 1;
+    }
+    if (!p->tiles1_ntc.empty()) {
+      DevPlan fb = dp;
+      fb.tiles1 = p->d_tiles1_ntc;
+      DISPATCH_R(p->R, {
+        if (fuse_add) {
+          if (set_smem(k_p_from_m<RR, true>, p->smem1)) return 1;
+          k_p_from_m<RR, true><<<(unsigned)p->tiles1_ntc.size(), kThreads, p->smem1, s>>>(fb, p->slot, q_mem, p_mem, q_div);
+        } else {
+          if (set_smem(k_p_from_m<RR, false>, p->smem1)) return 1;
+          k_p_from_m<RR, false><<<(unsigned)p->tiles1_ntc.size(), kThreads, p->smem1, s>>>(fb, p->slot, q_mem, p_mem, q_div);
+        }
+      });
+      if (check_launch("k_p_from_m")) return 1;
+    }
+    return 0;
+  }
   if (fuse_add ? p->stream1f_now : p->stream1_now) {
     StreamPlan sp{p->d_tasks1, p->d_counters + 2 * (p->seq1++ % kCtrRing), (int)p->tasks1.size(), p->ring_slot_bytes1, p->ring_slots1, p->q_bytes, p->d_dbg,
                   p->d_vtiles, flat, fold ? (int)p->vtiles.size() : 0, fold ? (fuse_add ? 2 : 1) : 0, 1.0f,
                   p->d_direct_ids, p->d_direct_row_pre, (int)p->direct_ids.size(), p->split_max_sub};
+    // peer: Q is summed over the ranks first, in the kernel's prologue when its grid is co-resident (one CTA per SM)
+    if (peer && p->stream_grid > p->sm_count) {
+      if (peer_reduce_standalone(peer, 1, const_cast<float*>(q_mem), p->q_total, (float)peer->world, 0, s)) return 1;
+      peer = nullptr;
+    }
+    const PeerQ pq = peer_q_args(p, peer, const_cast<float*>(q_mem));
     DISPATCH_R(p->R, {
       if (fuse_add) {
         if (set_smem(k_p_from_m_stream<RR, true>, p->stream_smem)) return 1;
-        CU(launch_ex(k_p_from_m_stream<RR, true>, dim3(p->stream_grid), dim3(kStreamThreads), p->stream_smem, s, 1, p->pdl, dp, p->slot, sp, q_mem, p_mem, q_div));
+        CU(launch_ex(k_p_from_m_stream<RR, true>, dim3(p->stream_grid), dim3(kStreamThreads), p->stream_smem, s, 1, p->pdl, dp, p->slot, sp, q_mem, p_mem, q_div, pq));
       } else {
         if (set_smem(k_p_from_m_stream<RR, false>, p->stream_smem)) return 1;
-        CU(launch_ex(k_p_from_m_stream<RR, false>, dim3(p->stream_grid), dim3(kStreamThreads), p->stream_smem, s, 1, p->pdl, dp, p->slot, sp, q_mem, p_mem, q_div));
+        CU(launch_ex(k_p_from_m_stream<RR, false>, dim3(p->stream_grid), dim3(kStreamThreads), p->stream_smem, s, 1, p->pdl, dp, p->slot, sp, q_mem, p_mem, q_div, pq));
       }
     });
     if (check_launch("k_p_from_m_stream")) return 1;
@@ -915,6 +1034,7 @@ static int p_from_m_impl(psgd_plan* p, float* p_mem, const float* q_mem, int fus
     }
     return 0;
   }
+  if (peer && peer_reduce_standalone(peer, 1, const_cast<float*>(q_mem), p->q_total, (float)peer->world, 0, s)) return 1;
   DISPATCH_R(p->R, {
     if (fuse_add) {
       if (set_smem(k_p_from_m<RR, true>, p->smem1)) return 1;
@@ -928,6 +1048,10 @@ static int p_from_m_impl(psgd_plan* p, float* p_mem, const float* q_mem, int fus
 }
 
 int psgd_orthogonalize(psgd_plan* p, float* p_mem, float n_workers, psgd_stream stream) {
+  return orth_impl(p, p_mem, n_workers, stream);
+}
+
+static int orth_impl(psgd_plan* p, float* p_mem, float n_workers, psgd_stream stream) {
   if (need_device(p)) return 1;
   if (p->n_mat == 0) return 0;
   if (!p_mem) return fail("psgd_orthogonalize: null p_mem");
@@ -935,6 +1059,7 @@ int psgd_orthogonalize(psgd_plan* p, float* p_mem, float n_workers, psgd_stream 
   CU(cudaSetDevice(p->device));
   cudaStream_t s = (cudaStream_t)stream;
   const DevPlan dp = dev_plan(p);
+  if (p->orth_small.empty() && p->orth_tall.empty() && p->orth_generic.empty()) return 0;
   PhaseScope ts(p, PSGD_PHASE_ORTH, s);
   // The small matrices (one CTA each) share the launch of the tall ones (one cluster each) when the whole thing
   // fits a single wave of clusters; a big population of small matrices keeps its own plain launch, where no SM is
@@ -994,7 +1119,7 @@ int psgd_q_from_mt(psgd_plan* p, const float* p_mem, float* q_mem, void* workspa
     const unsigned grid = (unsigned)p->tiles3.size();
     DISPATCH_R(p->R, {
       if (set_smem(k_q_from_mt<RR>, p->smem3)) return 1;
-      CU(launch_ex(k_q_from_mt<RR>, dim3(grid), dim3(kThreads3), p->smem3, s, 1, p->pdl, dp, p->slot, p_mem, (float*)ws, q_mem, fold ? p->d_ctr3 : (int*)nullptr));
+      CU(launch_ex(k_q_from_mt<RR>, dim3(grid), dim3(kThreads3), p->smem3, s, 1, p->pdl, dp, p->slot, p_mem, (float*)ws, q_mem, fold ? p->d_ctr3 : (int*)nullptr, (p->tc && (p->tc_mask & 2) && p->tc_now) ? 1 : 0));
     });
     if (check_launch("k_q_from_mt")) return 1;
   }
@@ -1007,7 +1132,7 @@ int psgd_q_from_mt(psgd_plan* p, const float* p_mem, float* q_mem, void* workspa
 }
 
 static int finalize_impl(psgd_plan* p, const float* p_mem, const float* q_mem, float n_workers, const float* flat,
-                         psgd_stream stream);
+                         psgd_stream stream, psgd_peer* peer = nullptr);
 
 int psgd_finalize(psgd_plan* p, const float* p_mem, const float* q_mem, float n_workers, psgd_stream stream) {
   return finalize_impl(p, p_mem, q_mem, n_workers, nullptr, stream);
@@ -1021,9 +1146,10 @@ int psgd_finalize_unpack(psgd_plan* p, const float* p_mem, const float* q_mem, f
 }
 
 static int finalize_impl(psgd_plan* p, const float* p_mem, const float* q_mem, float n_workers, const float* flat,
-                         psgd_stream stream) {
+                         psgd_stream stream, psgd_peer* peer) {
   if (need_device(p) || need_ptrs(p)) return 1;
-  const bool fold = flat && p->v_total && !p->tiles4.empty() && p->stream4_now;
+  const bool tc4 = p->tc && (p->tc_mask & 4) && p->tc_now;
+  const bool fold = flat && p->v_total && !p->tiles4.empty() && !tc4 && p->stream4_now;
   if (flat && p->v_total && !fold) {  // no streamed launch to ride on: separate scatter
     if (psgd_finish(p, flat, nullptr, n_workers, stream)) return 1;
   }
@@ -1035,13 +1161,44 @@ static int finalize_impl(psgd_plan* p, const float* p_mem, const float* q_mem, f
   const DevPlan dp = dev_plan(p);
   const unsigned grid = (unsigned)p->tiles4.size();
   PhaseScope ts(p, PSGD_PHASE_FINALIZE, s);
+  if (tc4) {  // ranks 16 / 32: tensor pipe
+    if (peer && peer_reduce_standalone(peer, 1, const_cast<float*>(q_mem), p->q_total, (float)peer->world, 0, s)) return 1;
+    if (!p->tiles4_tc.empty()) {
+      DevPlan tp = dp;
+      tp.tiles4 = p->d_tiles4_tc;
+      const unsigned g = (unsigned)p->tiles4_tc.size();
+      if (p->R == 16) {
+        if (set_smem(k_finalize_tc<16>, p->tc_smem4)) return 1;
+        k_finalize_tc<16><<<g, kTcThreads, p->tc_smem4, s>>>(tp, p->slot, p_mem, q_mem, n_workers, p->tc_wc4);
+      } else {
+        if (set_smem(k_finalize_tc<32>, p->tc_smem4)) return 1;
+        k_finalize_tc<32><<<g, kTcThreads, p->tc_smem4, s>>>(tp, p->slot, p_mem, q_mem, n_workers, p->tc_wc4);
+      }
+      if (check_launch("k_finalize_tc")) return 1;
+    }
+    if (!p->tiles4_ntc.empty()) {
+      DevPlan fb = dp;
+      fb.tiles4 = p->d_tiles4_ntc;
+      DISPATCH_R(p->R, {
+        if (set_smem(k_finalize<RR>, p->smem4)) return 1;
+        k_finalize<RR><<<(unsigned)p->tiles4_ntc.size(), kThreads, p->smem4, s>>>(fb, p->slot, p_mem, q_mem, n_workers);
+      });
+      if (check_launch("k_finalize")) return 1;
+    }
+    return 0;
+  }
   if (p->stream4_now) {
     StreamPlan sp{p->d_tasks4, p->d_counters + 2 * kCtrRing + 2 * (p->seq4++ % kCtrRing), (int)p->tasks4.size(), p->ring_slot_bytes, p->ring_slots, p->q_bytes, nullptr,
                   p->d_vtiles, const_cast<float*>(flat), fold ? (int)p->vtiles.size() : 0, fold ? 3 : 0, n_workers,
                   p->d_direct_ids, p->d_direct_row_pre, (int)p->direct_ids.size(), 0};
+    if (peer && p->stream_grid > p->sm_count) {
+      if (peer_reduce_standalone(peer, 1, const_cast<float*>(q_mem), p->q_total, (float)peer->world, 0, s)) return 1;
+      peer = nullptr;
+    }
+    const PeerQ pq = peer_q_args(p, peer, const_cast<float*>(q_mem));
     DISPATCH_R(p->R, {
       if (set_smem(k_finalize_stream<RR>, p->stream_smem)) return 1;
-      CU(launch_ex(k_finalize_stream<RR>, dim3(p->stream_grid), dim3(kStreamThreads), p->stream_smem, s, 1, p->pdl, dp, p->slot, sp, p_mem, q_mem, n_workers));
+      CU(launch_ex(k_finalize_stream<RR>, dim3(p->stream_grid), dim3(kStreamThreads), p->stream_smem, s, 1, p->pdl, dp, p->slot, sp, p_mem, q_mem, n_workers, pq));
     });
     if (check_launch("k_finalize_stream")) return 1;
     if (!p->tiles4_fb.empty()) {
@@ -1055,6 +1212,7 @@ static int finalize_impl(psgd_plan* p, const float* p_mem, const float* q_mem, f
     }
     return 0;
   }
+  if (peer && peer_reduce_standalone(peer, 1, const_cast<float*>(q_mem), p->q_total, (float)peer->world, 0, s)) return 1;
   DISPATCH_R(p->R, {
     if (set_smem(k_finalize<RR>, p->smem4)) return 1;
     k_finalize<RR><<<grid, kThreads, p->smem4, s>>>(dp, p->slot, p_mem, q_mem, n_workers);
@@ -1074,6 +1232,168 @@ int psgd_finish(psgd_plan* p, const float* flat, float* q_mem, float n_workers, 
   const unsigned grid = (unsigned)(nvt + (size_t)((qn + kVecTileElems - 1) / kVecTileElems));
   k_finish<<<grid, kThreads, 0, s>>>(dev_plan(p), p->slot, flat, (int)nvt, q_mem, qn, n_workers);
   return check_launch("k_finish");
+}
+
+// ---- all-reduces taken into the kernels (SURVEY f-2): symmetric-memory handle and the peer-aware phase calls ----------
+
+static PeerLoad peer_load(psgd_peer* peer, int which) {
+  PeerLoad pm = which == 0 ? peer->pf : peer->q;
+  pm.epoch = which == 0 ? ++peer->epoch_pf : ++peer->epoch_q;
+  return pm;
+}
+
+static PeerQ peer_q_args(psgd_plan* p, psgd_peer* peer, float* q_mem) {
+  PeerQ pq{};
+  pq.pm.mode = kPeerOff;
+  if (!peer) return pq;
+  pq.pm = peer_load(peer, 1);
+  pq.q_out = q_mem;
+  pq.n = p->q_total;
+  pq.div = (float)peer->world;
+  pq.gsync = peer->d_gsync;
+  peer->gseq += (unsigned)p->stream_grid;
+  pq.gtarget = peer->gseq;
+  return pq;
+}
+
+static int peer_reduce_standalone(psgd_peer* peer, int which, float* out, long long n, float div, long long div_from,
+                                  cudaStream_t s) {
+  if (n <= 0) return 0;
+  const PeerLoad pm = peer_load(peer, which);
+  const unsigned grid = (unsigned)std::min<long long>(128, std::max<long long>(1, (n + kThreads * 4 - 1) / (kThreads * 4)));
+  k_peer_reduce_to_local<<<grid, kThreads, 0, s>>>(pm, out, n, div, div_from);
+  return check_launch("k_peer_reduce_to_local");
+}
+
+int psgd_peer_create(int world, int rank, int device, const void* const* pf_bufs, void* const* pf_signals,
+                     const void* pf_multicast, const void* const* q_bufs, void* const* q_signals,
+                     const void* q_multicast, int slot0, int mode, psgd_peer** out) {
+  if (!out) return fail("out is null");
+  *out = nullptr;
+  if (world < 2 || world > kMaxPeers) return fail("psgd_peer_create: world size %d not in 2..%d", world, kMaxPeers);
+  if (rank < 0 || rank >= world) return fail("psgd_peer_create: bad rank");
+  if (device < 0) return fail("psgd_peer_create: needs a CUDA device");
+  if (mode != kPeerMultimem && mode != kPeerPull) return fail("psgd_peer_create: mode must be 1 (multimem) or 2 (pull)");
+  if (!pf_bufs || !pf_signals || !q_bufs || !q_signals) return fail("psgd_peer_create: null pointer array");
+  if (mode == kPeerMultimem && (!pf_multicast || !q_multicast)) return fail("psgd_peer_create: multimem mode needs the multicast addresses");
+  if (slot0 < 0) return fail("psgd_peer_create: bad signal slot");
+  psgd_peer* h = new psgd_peer();
+  h->device = device; h->world = world; h->rank = rank; h->mode = mode;
+  for (int w = 0; w < 2; ++w) {
+    PeerLoad& pm = w == 0 ? h->pf : h->q;
+    const void* const* bufs = w == 0 ? pf_bufs : q_bufs;
+    void* const* sigs = w == 0 ? pf_signals : q_signals;
+    for (int r = 0; r < world; ++r) {
+      if (!bufs[r] || !sigs[r] || ((uintptr_t)bufs[r] & 15)) {
+        delete h;
+        return fail("psgd_peer_create: rank %d has a null or misaligned (16 bytes) buffer", r);
+      }
+      pm.in[r] = (const float*)bufs[r];
+      pm.sig[r] = (unsigned*)sigs[r];
+    }
+    pm.mc = (const float*)(w == 0 ? pf_multicast : q_multicast);
+    if ((uintptr_t)pm.mc & 15) { delete h; return fail("psgd_peer_create: multicast address must be 16-byte aligned"); }
+    pm.rank = rank; pm.world = world; pm.slot0 = slot0; pm.mode = mode; pm.epoch = 0; pm.pad_ = 0;
+  }
+  if (cudaSetDevice(device) != cudaSuccess || cudaMalloc((void**)&h->d_gsync, sizeof(unsigned)) != cudaSuccess ||
+      cudaMemset(h->d_gsync, 0, sizeof(unsigned)) != cudaSuccess) {
+    delete h;
+    return fail("psgd_peer_create: device set-up failed");
+  }
+  *out = h;
+  return 0;
+}
+
+int psgd_peer_destroy(psgd_peer* h) {
+  if (!h) return 0;
+  cudaSetDevice(h->device);
+  cudaFree(h->d_gsync);
+  delete h;
+  return 0;
+}
+
+int psgd_p_from_m_peer(psgd_plan* p, psgd_peer* peer, float* p_mem, float* q_mem, int fuse_add, psgd_stream stream) {
+  if (!peer) return fail("psgd_p_from_m_peer: null peer handle");
+  if (need_device(p) || need_ptrs(p)) return 1;
+  if (p->stream_grid > 0 && peer->device != p->device) return fail("psgd_p_from_m_peer: plan and peer handle are on different devices");
+  return p_from_m_impl(p, p_mem, q_mem, fuse_add, 1.0f, nullptr, stream, peer);
+}
+
+int psgd_finalize_peer(psgd_plan* p, psgd_peer* peer, const float* p_mem, float* q_mem, const float* flat,
+                       psgd_stream stream) {
+  if (!peer) return fail("psgd_finalize_peer: null peer handle");
+  if (need_device(p) || need_ptrs(p)) return 1;
+  if (peer->device != p->device) return fail("psgd_finalize_peer: plan and peer handle are on different devices");
+  if (p->v_total && !flat) return fail("psgd_finalize_peer: flat is null");
+  if (p->tiles4.empty()) {  // no matrix at all: only the scatter of the (already averaged) flat buffer is left
+    return psgd_finish(p, flat, nullptr, 1.0f, stream);
+  }
+  // q_mem holds the MEAN once the kernel's prologue (or the stand-alone reduction) has run: staged with a world of 1
+  return finalize_impl(p, p_mem, q_mem, 1.0f, flat, stream, peer);
+}
+
+int psgd_orthogonalize_peer(psgd_plan* p, psgd_peer* peer, float* p_mem, float* flat_out, psgd_stream stream) {
+  if (!peer) return fail("psgd_orthogonalize_peer: null peer handle");
+  if (need_device(p)) return 1;
+  if (peer->device != p->device) return fail("psgd_orthogonalize_peer: plan and peer handle are on different devices");
+  const bool want_flat = flat_out != nullptr && p->v_total > 0;
+  if (p->n_mat == 0 && !want_flat) return 0;
+  if (p->n_mat && !p_mem) return fail("psgd_orthogonalize_peer: null p_mem");
+  CU(cudaSetDevice(p->device));
+  cudaStream_t s = (cudaStream_t)stream;
+  const float world = (float)peer->world;
+  const int n_small = (int)p->orth_small.size(), n_tall = (int)p->orth_tall.size();
+  // what the register-resident kernels cannot take (very tall matrices, rank 32) goes through the stand-alone
+  // reduction into the local buffers followed by the ordinary Gram-Schmidt launches
+  if (!p->orth_generic.empty() || p->R > 16 || (n_small == 0 && n_tall == 0)) {
+    if (p->p_total && peer_reduce_standalone(peer, 0, p_mem, p->p_total, 1.0f, 0, s)) return 1;
+    if (want_flat) {
+      // the flat part behind P: a second reduction with its own barrier epoch (scalar loads: any alignment)
+      PeerLoad pm = peer_load(peer, 0);
+      for (int r = 0; r < peer->world; ++r) pm.in[r] += p->p_total;
+      if (pm.mc) pm.mc += p->p_total;
+      const unsigned grid = (unsigned)std::min<long long>(64, std::max<long long>(1, (p->v_total + kThreads - 1) / kThreads));
+      k_peer_reduce_to_local<<<grid, kThreads, 0, s>>>(pm, flat_out, p->v_total, world, 0);
+      if (check_launch("k_peer_reduce_to_local")) return 1;
+    }
+    return orth_impl(p, p_mem, world, stream);
+  }
+  PhaseScope ts(p, PSGD_PHASE_ORTH, s);
+  const DevPlan dp = dev_plan(p);
+  const PeerLoad pm = peer_load(peer, 0);
+  PeerFlat pf{};
+  pf.out = want_flat ? flat_out : nullptr;
+  pf.sym_off = p->p_total;
+  pf.n = want_flat ? p->v_total : 0;
+  pf.div = world;
+  const int n_flat_ctas = want_flat ? (int)((p->v_total + kPeerFlatPerCta - 1) / kPeerFlatPerCta) : 0;
+  const int tcs = p->orth_tall_cluster;
+  const bool merged = n_tall > 0 && (n_tall + (n_small + n_flat_ctas + tcs - 1) / tcs) * tcs <= std::max(p->orth_merge_max_ctas, 148);
+  if (n_tall == 0 || !merged) {  // small matrices (and, without tall ones, the flat buffer) in a plain launch
+    const bool flat_here = n_tall == 0;
+    PeerFlat pf_small = flat_here ? pf : PeerFlat{};
+    const unsigned grid = (unsigned)(n_small + (flat_here ? n_flat_ctas : 0));
+    if (grid) {
+      if (p->R <= 8) {
+        DISPATCH_R8(p->R, { CU(launch_ex(k_orth_small_peer<RR, 4>, dim3(grid), dim3(kOrthSmallThreads), 0, s, 1, p->pdl, dp, (const int*)p->d_orth_small, n_small, p_mem, world, pm, pf_small)); });
+      } else {
+        CU(launch_ex(k_orth_small_peer<16, 2>, dim3(grid), dim3(kOrthSmallThreads), 0, s, 1, p->pdl, dp, (const int*)p->d_orth_small, n_small, p_mem, world, pm, pf_small));
+      }
+      if (check_launch("k_orth_small_peer")) return 1;
+    }
+  }
+  if (n_tall) {
+    const int n_ride = merged ? n_small : 0;
+    const dim3 grid((unsigned)(n_tall + (n_ride + n_flat_ctas + tcs - 1) / tcs) * tcs);
+    if (p->R <= 8) {
+      DISPATCH_R8(p->R, { CU(launch_ex(k_orth_tall_peer<RR, 4>, grid, dim3(kOrthSmallThreads), 0, s, tcs, p->pdl, dp, (const int*)p->d_orth_tall, n_tall, (const int*)p->d_orth_small, n_ride, p_mem, world, pm, pf)); });
+    } else {
+      CU(cudaFuncSetAttribute((const void*)k_orth_tall_peer<16, 2>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+      CU(launch_ex(k_orth_tall_peer<16, 2>, grid, dim3(kOrthSmallThreads), 0, s, tcs, p->pdl, dp, (const int*)p->d_orth_tall, n_tall, (const int*)p->d_orth_small, n_ride, p_mem, world, pm, pf));
+    }
+    if (check_launch("k_orth_tall_peer")) return 1;
+  }
+  return 0;
 }
 
 int psgd_timing_enable(psgd_plan* p, int on) {

@@ -1,12 +1,14 @@
 // Shared device-side types and small helpers for the PowerSGD kernels (sm_100a).
 #pragma once
 #include <cuda_runtime.h>
+#include <cstdio>
 #include <stdint.h>
 
 namespace psgd {
 
 constexpr int kThreads = 256;      // CTA size of the streaming kernels (8 warps)
 constexpr int kWarps = kThreads / 32;
+constexpr int kConsumerWarps = 8;   // consumer warps of the streamed kernels (psgd_stream.cuh); warp 8 is the producer
 constexpr int kOrthThreads = 512;  // CTA size of the generic (global-memory) Gram-Schmidt kernel
 constexpr int kOrthSmallThreads = 1024;  // CTA size of the register-resident Gram-Schmidt kernels
 constexpr int kOrthCluster = 8;    // CTAs per matrix (one thread-block cluster)
@@ -88,6 +90,115 @@ __device__ __forceinline__ void pdl_launch_dependents() {
 }
 __device__ __forceinline__ void pdl_wait() {
   asm volatile("griddepcontrol.wait;" ::: "memory");
+}
+
+// named barrier over the consumer warps of a streamed kernel only (threads 0 .. 255)
+__device__ __forceinline__ void consumer_sync() {
+  asm volatile("bar.sync 1, %0;" ::"n"(kConsumerWarps * 32) : "memory");
+}
+
+// ---- peer (NVLink) memory: flags, loads, in-switch reductions --------------------------------------------------
+constexpr int kMaxPeers = 8;
+struct PeerArgs {
+  const float* in[kMaxPeers];   // input buffer of every rank, mapped into this process
+  unsigned* sig[kMaxPeers];     // signal pad of every rank (uint32 slots), mapped into this process
+};
+
+__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
+  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ unsigned ld_acquire_gpu(const unsigned* p) {
+  unsigned v;
+  asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float4 ld_sys4(const float* p) {
+  float4 v;
+  asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
+  return v;
+}
+__device__ __forceinline__ float ld_sys1(const float* p) {
+  float v;
+  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
+  return v;
+}
+
+__device__ __forceinline__ float4 mm_ld_reduce4(const float* mc) {
+  float4 v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
+  return v;
+}
+__device__ __forceinline__ void mm_st4(float* mc, float4 v) {
+  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z),
+               "f"(v.w) : "memory");
+}
+
+// all threads of the CTA return once every rank has posted `epoch` in this rank's flags[0 .. world)
+__device__ __forceinline__ void peer_flags_wait(const unsigned* flags, int world, unsigned epoch, int rank, int which) {
+  if ((int)threadIdx.x < world) {
+    const long long t0 = clock64();
+    while ((int)(ld_acquire_sys(flags + threadIdx.x) - epoch) < 0) {
+      if (clock64() - t0 > 20000000000LL) {  // ~10 s: a crashed peer must not hang the GPU
+        printf("psgd k_peer_allreduce_mc: rank %d timed out waiting for rank %d (barrier %d, epoch %u)\n", rank,
+               (int)threadIdx.x, which, epoch);
+        __trap();
+      }
+    }
+  }
+  __syncthreads();
+}
+
+__device__ __forceinline__ float mm_ld_reduce1(const float* mc) {
+  float v;
+  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.f32 %0, [%1];" : "=f"(v) : "l"(mc) : "memory");
+  return v;
+}
+
+// What a kernel needs to read a buffer "summed over all ranks" (SUM all-reduce on load) from symmetric memory: every
+// rank's copy as mapped into this process, the NVSwitch multicast address of the same buffer (or null), this rank's
+// signal pad and everybody else's.  mode 1: one multimem.ld_reduce per element (the switch adds the copies); mode 2:
+// one load per rank, added in rank order (bit-identical on every rank by construction, needs no multicast mapping).
+// Peer data is only ever touched with plain / multimem loads and stores.
+struct PeerLoad {
+  const float* in[kMaxPeers];
+  unsigned* sig[kMaxPeers];
+  const float* mc;
+  int rank, world, slot0, mode;
+  unsigned epoch;
+  int pad_;
+};
+enum { kPeerOff = 0, kPeerMultimem = 1, kPeerPull = 2 };
+
+// "This rank's input is complete" to every peer (one CTA does it, after its own dependency wait), then every CTA
+// waits until all ranks have said so.  All threads of the CTA must call it (it ends in __syncthreads()).
+__device__ __forceinline__ void peer_barrier(const PeerLoad& pm, bool announce) {
+  if (announce && (int)threadIdx.x < pm.world) {
+    __threadfence_system();
+    st_release_sys(pm.sig[threadIdx.x] + pm.slot0 + pm.rank, pm.epoch);
+  }
+  peer_flags_wait(pm.sig[pm.rank] + pm.slot0, pm.world, pm.epoch, pm.rank, 0);
+}
+__device__ __forceinline__ float4 peer_sum4(const PeerLoad& pm, long long e) {  // e % 4 == 0, 16-byte aligned buffers
+  if (pm.mode == kPeerMultimem) return mm_ld_reduce4(pm.mc + e);
+  float4 s = ld_sys4(pm.in[0] + e);
+  for (int r = 1; r < pm.world; ++r) {
+    const float4 v = ld_sys4(pm.in[r] + e);
+    s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+  }
+  return s;
+}
+__device__ __forceinline__ float peer_sum1(const PeerLoad& pm, long long e) {
+  if (pm.mode == kPeerMultimem) return mm_ld_reduce1(pm.mc + e);
+  float s = ld_sys1(pm.in[0] + e);
+  for (int r = 1; r < pm.world; ++r) s += ld_sys1(pm.in[r] + e);
+  return s;
 }
 
 // ---- memory helpers -------------------------------------------------------------------

@@ -9,6 +9,7 @@
 #include <cooperative_groups.h>
 
 #include "psgd_common.cuh"
+#include "psgd_tc.cuh"
 
 namespace psgd {
 namespace cg = cooperative_groups;
@@ -274,21 +275,24 @@ __device__ __forceinline__ void orth_body(float* __restrict__ P, int n, int r, f
 // runs a whole matrix in one CTA with block barriers only; csize > 1 spreads one tall matrix over a
 // thread-block cluster and exchanges the partials through distributed shared memory.  All sums are
 // formed in a fixed order (xor-shuffle trees, then CTA rank order), so results are deterministic.
+//   wsum: 32 * R floats, part: 2 * kOrthClusterMax * R floats, both 16-byte aligned shared memory
+// pm != nullptr: the rows are read "summed over all ranks" from symmetric memory (element offset sym_off of the
+// buffer pm describes: the SUM all-reduce of reducer.py:126 happens on load), the result goes to the local P.
 template <int R, int RPT>
 __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r, float world,
-                                            int crank, int csize) {
+                                            int crank, int csize, float* wsum, float* part,
+                                            const PeerLoad* pm = nullptr, long long sym_off = 0) {
   constexpr int LPV = 32 / R;  // lanes per value after a warp_fold<R>
-  __shared__ __align__(16) float wsum[32][R];
-  __shared__ __align__(16) float part[2][kOrthClusterMax][R];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nthr = blockDim.x, nwarp = nthr >> 5;
   const int per = (n + csize - 1) / csize;
   const int lo = crank * per;
   const int hi = (lo + per < n) ? lo + per : n;
+  auto cta_sync = [] { __syncthreads(); };
 
   // IEEE fp32 division costs ~40 instructions; one reciprocal per scale factor and multiplies instead
   // (exact for power-of-two worker counts, otherwise within 1 ulp of the reference's true division)
-  const bool vec4 = (R % 4 == 0) && (r == R) && ((reinterpret_cast<uintptr_t>(P) & 15) == 0);
+  const bool vec4 = (R % 4 == 0) && (r == R) && ((reinterpret_cast<uintptr_t>(P) & 15) == 0) && ((sym_off & 3) == 0);
   float v[RPT][R];
 #pragma unroll
   for (int k = 0; k < RPT; ++k) {
@@ -297,12 +301,18 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
 #pragma unroll
       for (int c = 0; c < R; c += 4) {
         float4 t = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (row < hi) t = *reinterpret_cast<const float4*>(P + (size_t)row * R + c);
+        if (row < hi) {
+          if (pm) t = peer_sum4(*pm, sym_off + (long long)row * R + c);
+          else t = __ldcg(reinterpret_cast<const float4*>(P + (size_t)row * R + c));
+        }
         v[k][c] = t.x; v[k][(c + 1) % R] = t.y; v[k][(c + 2) % R] = t.z; v[k][(c + 3) % R] = t.w;
       }
     } else {
 #pragma unroll
-      for (int j = 0; j < R; ++j) v[k][j] = (row < hi && j < r) ? P[(size_t)row * r + j] : 0.f;
+      for (int j = 0; j < R; ++j) {
+        v[k][j] = 0.f;
+        if (row < hi && j < r) v[k][j] = pm ? peer_sum1(*pm, sym_off + (long long)row * r + j) : __ldcg(P + (size_t)row * r + j);
+      }
     }
   }
   if (world != 1.0f) {
@@ -332,28 +342,28 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
         for (int j = 0; j < R; ++j) s[j] = fmaf(v[k][0], v[k][j], s[j]);
       {
         const float w = warp_fold<R>(s, lane);
-        if ((lane % LPV) == 0) wsum[warp][lane / LPV] = w;
+        if ((lane % LPV) == 0) wsum[warp * R + lane / LPV] = w;
       }
-      __syncthreads();
+      cta_sync();
       const int par = i & 1;
       if (warp == 0) {
         float t[R];
 #pragma unroll
-        for (int j = 0; j < R; ++j) t[j] = (lane < nwarp) ? wsum[lane][j] : 0.f;
+        for (int j = 0; j < R; ++j) t[j] = (lane < nwarp) ? wsum[lane * R + j] : 0.f;
         const float w = warp_fold<R>(t, lane);
         if ((lane % LPV) == 0) {
           const int j = lane / LPV;
           if (csize > 1) {
             for (int dst = 0; dst < csize; ++dst) {
-              float* remote = cg::this_cluster().map_shared_rank(&part[0][0][0], dst);
+              float* remote = cg::this_cluster().map_shared_rank(part, dst);
               remote[(par * kOrthClusterMax + crank) * R + j] = w;
             }
           } else {
-            part[par][0][j] = w;
+            part[(par * kOrthClusterMax) * R + j] = w;
           }
         }
       }
-      if (csize > 1) cg::this_cluster().sync(); else __syncthreads();
+      if (csize > 1) cg::this_cluster().sync(); else cta_sync();
       float tot[R];
 #pragma unroll
       for (int j = 0; j < R; ++j) tot[j] = 0.f;
@@ -361,12 +371,12 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
         if (R % 4 == 0) {
 #pragma unroll
           for (int j = 0; j < R; j += 4) {
-            const float4 q = *reinterpret_cast<const float4*>(&part[par][c][j]);
+            const float4 q = *reinterpret_cast<const float4*>(part + (par * kOrthClusterMax + c) * R + j);
             tot[j] += q.x; tot[(j + 1) % R] += q.y; tot[(j + 2) % R] += q.z; tot[(j + 3) % R] += q.w;
           }
         } else {
 #pragma unroll
-          for (int j = 0; j < R; ++j) tot[j] += part[par][c][j];
+          for (int j = 0; j < R; ++j) tot[j] += part[(par * kOrthClusterMax + c) * R + j];
         }
       }
       const float inv = 1.0f / (sqrtf(tot[0]) + 1e-8f);  // eps outside the root, reducer.py:186
@@ -405,28 +415,28 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
         for (int j = i; j < R; ++j) s[j] = fmaf(v[k][i], v[k][j], s[j]);
       {
         const float w = warp_fold<R>(s, lane);
-        if ((lane % LPV) == 0) wsum[warp][lane / LPV] = w;
+        if ((lane % LPV) == 0) wsum[warp * R + lane / LPV] = w;
       }
-      __syncthreads();
+      cta_sync();
       const int par = i & 1;
       if (warp == 0) {
         float t[R];
 #pragma unroll
-        for (int j = 0; j < R; ++j) t[j] = (lane < nwarp) ? wsum[lane][j] : 0.f;
+        for (int j = 0; j < R; ++j) t[j] = (lane < nwarp) ? wsum[lane * R + j] : 0.f;
         const float w = warp_fold<R>(t, lane);
         if ((lane % LPV) == 0) {
           const int j = lane / LPV;
           if (csize > 1) {
             for (int dst = 0; dst < csize; ++dst) {
-              float* remote = cg::this_cluster().map_shared_rank(&part[0][0][0], dst);
+              float* remote = cg::this_cluster().map_shared_rank(part, dst);
               remote[(par * kOrthClusterMax + crank) * R + j] = w;
             }
           } else {
-            part[par][0][j] = w;
+            part[(par * kOrthClusterMax) * R + j] = w;
           }
         }
       }
-      if (csize > 1) cg::this_cluster().sync(); else __syncthreads();
+      if (csize > 1) cg::this_cluster().sync(); else cta_sync();
       float tot[R];
 #pragma unroll
       for (int j = 0; j < R; ++j) tot[j] = 0.f;
@@ -434,12 +444,12 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
         if (R % 4 == 0) {
 #pragma unroll
           for (int j = 0; j < R; j += 4) {
-            const float4 q = *reinterpret_cast<const float4*>(&part[par][c][j]);
+            const float4 q = *reinterpret_cast<const float4*>(part + (par * kOrthClusterMax + c) * R + j);
             tot[j] += q.x; tot[(j + 1) % R] += q.y; tot[(j + 2) % R] += q.z; tot[(j + 3) % R] += q.w;
           }
         } else {
 #pragma unroll
-          for (int j = 0; j < R; ++j) tot[j] += part[par][c][j];
+          for (int j = 0; j < R; ++j) tot[j] += part[(par * kOrthClusterMax + c) * R + j];
         }
       }
       const float inv = 1.0f / (sqrtf(tot[i]) + 1e-8f);  // eps outside the root, reducer.py:186
@@ -478,10 +488,56 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
 template <int R, int RPT>
 __global__ void __launch_bounds__(kOrthSmallThreads)
 k_orth_small(DevPlan pl, const int* __restrict__ ids, float* __restrict__ p_mem, float world) {
+  __shared__ __align__(16) float wsum[32 * R];
+  __shared__ __align__(16) float part[2 * kOrthClusterMax * R];
   pdl_launch_dependents();
-  const MatDesc md = pl.mats[ids[blockIdx.x]];
+  const int mat = ids[blockIdx.x];
+  const MatDesc md = pl.mats[mat];
   pdl_wait();
-  orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, 0, 1);
+  orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, 0, 1, wsum, part);
+}
+
+// The flat <=1-D buffer travels behind P in the same symmetric buffer (reducer.py:131-133): CTAs past the matrices sum
+// it over the ranks, form the mean (reducer.py:167) and leave it in the local flat buffer.
+struct PeerFlat {
+  float* out;          // local flat buffer (mean over ranks); nullptr: nothing to do
+  long long sym_off;   // element offset of the flat part in the symmetric buffer (= sum n*r)
+  long long n;         // elements
+  float div;           // n_workers
+};
+constexpr int kPeerFlatPerCta = kOrthSmallThreads * 4;
+
+__device__ __forceinline__ void peer_flat_job(const PeerLoad& pm, const PeerFlat& pf, int idx) {
+  const long long e = (long long)idx * kPeerFlatPerCta + (long long)threadIdx.x * 4;
+  if (e >= pf.n) return;
+  if (e + 4 <= pf.n && ((pf.sym_off & 3) == 0) && ((reinterpret_cast<uintptr_t>(pf.out) & 15) == 0)) {
+    float4 v = peer_sum4(pm, pf.sym_off + e);
+    v.x = v.x / pf.div; v.y = v.y / pf.div; v.z = v.z / pf.div; v.w = v.w / pf.div;
+    *reinterpret_cast<float4*>(pf.out + e) = v;
+  } else {
+    for (long long k = e; k < e + 4 && k < pf.n; ++k) pf.out[k] = peer_sum1(pm, pf.sym_off + k) / pf.div;
+  }
+}
+
+// K2 with the P all-reduce on load (reducer.py:126-128 + 136-137 in one kernel): after its dependency wait the
+// grid tells every peer "my P is written" and waits for theirs (one flag barrier, no extra launch, no copy), then
+// every CTA reads its rows summed over the ranks.  One CTA per small matrix.
+template <int R, int RPT>
+__global__ void __launch_bounds__(kOrthSmallThreads)
+k_orth_small_peer(DevPlan pl, const int* __restrict__ ids, int n_small, float* __restrict__ p_mem, float world,
+                  PeerLoad pm, PeerFlat pf) {
+  __shared__ __align__(16) float wsum[32 * R];
+  __shared__ __align__(16) float part[2 * kOrthClusterMax * R];
+  pdl_launch_dependents();
+  pdl_wait();
+  peer_barrier(pm, blockIdx.x == 0);
+  if ((int)blockIdx.x < n_small) {
+    const int mat = ids[blockIdx.x];
+    const MatDesc md = pl.mats[mat];
+    orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, 0, 1, wsum, part, &pm, md.p_off);
+  } else if (pf.out) {
+    peer_flat_job(pm, pf, (int)blockIdx.x - n_small);
+  }
 }
 
 // one cluster per "tall" matrix (n <= cluster * blockDim * RPT).  When the plan also has small matrices and everything
@@ -491,23 +547,56 @@ template <int R, int RPT>
 __global__ void __launch_bounds__(kOrthSmallThreads)
 k_orth_tall(DevPlan pl, const int* __restrict__ ids, int n_tall, const int* __restrict__ small_ids, int n_small,
             float* __restrict__ p_mem, float world) {
+  __shared__ __align__(16) float wsum[32 * R];
+  __shared__ __align__(16) float part[2 * kOrthClusterMax * R];
   cg::cluster_group cluster = cg::this_cluster();
   const int csize = (int)cluster.num_blocks();
   const int cl = blockIdx.x / csize;
   pdl_launch_dependents();
   if (cl < n_tall) {
-    const MatDesc md = pl.mats[ids[cl]];
+    const int mat = ids[cl];
+    const MatDesc md = pl.mats[mat];
     pdl_wait();
-    orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, (int)cluster.block_rank(), csize);
+    orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, (int)cluster.block_rank(), csize, wsum, part);
   } else {
     const int idx = (cl - n_tall) * csize + (int)cluster.block_rank();
     if (idx >= n_small) {
       pdl_wait();  // every CTA waits: the grid must not be able to complete before its predecessor has
       return;
     }
-    const MatDesc md = pl.mats[small_ids[idx]];
+    const int mat = small_ids[idx];
+    const MatDesc md = pl.mats[mat];
     pdl_wait();
-    orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, 0, 1);
+    orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, 0, 1, wsum, part);
+  }
+}
+
+// tall matrices one cluster each, small ones in container clusters, then the flat buffer (see k_orth_small_peer)
+template <int R, int RPT>
+__global__ void __launch_bounds__(kOrthSmallThreads)
+k_orth_tall_peer(DevPlan pl, const int* __restrict__ ids, int n_tall, const int* __restrict__ small_ids, int n_small,
+                 float* __restrict__ p_mem, float world, PeerLoad pm, PeerFlat pf) {
+  __shared__ __align__(16) float wsum[32 * R];
+  __shared__ __align__(16) float part[2 * kOrthClusterMax * R];
+  cg::cluster_group cluster = cg::this_cluster();
+  const int csize = (int)cluster.num_blocks();
+  const int cl = blockIdx.x / csize;
+  pdl_launch_dependents();
+  pdl_wait();
+  peer_barrier(pm, blockIdx.x == 0);
+  if (cl < n_tall) {
+    const int mat = ids[cl];
+    const MatDesc md = pl.mats[mat];
+    orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, (int)cluster.block_rank(), csize, wsum, part, &pm, md.p_off);
+  } else {
+    const int idx = (cl - n_tall) * csize + (int)cluster.block_rank();
+    if (idx < n_small) {
+      const int mat = small_ids[idx];
+      const MatDesc md = pl.mats[mat];
+      orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, 0, 1, wsum, part, &pm, md.p_off);
+    } else if (pf.out) {
+      peer_flat_job(pm, pf, idx - n_small);
+    }
   }
 }
 
@@ -563,7 +652,7 @@ __device__ __forceinline__ void q_tile(const MatDesc& md, const ColTile& t, cons
     const int total = nrows * R;
     for (int e = tid; e < total; e += NT) {
       const int i = e / R, c = e % R;
-      Ps[e] = (c < r) ? __ldg(src + (size_t)i * r + c) : 0.f;
+      Ps[e] = (c < r) ? __ldcg(src + (size_t)i * r + c) : 0.f;
     }
   }
   __syncthreads();
@@ -652,7 +741,7 @@ __device__ __forceinline__ void q_tile(const MatDesc& md, const ColTile& t, cons
 template <int R>
 __global__ void __launch_bounds__(kThreads3, (R <= 8) ? kMinBlocks3 : (R == 16) ? 2 : 1)
 k_q_from_mt(DevPlan pl, PtrSlot ps, const float* __restrict__ p_mem, float* __restrict__ ws, float* __restrict__ q_mem,
-            int* __restrict__ done) {
+            int* __restrict__ done, int use_tc) {
   extern __shared__ __align__(16) float smem[];
   pdl_launch_dependents();
   const ColTile t = pl.tiles3[blockIdx.x];
@@ -661,7 +750,15 @@ k_q_from_mt(DevPlan pl, PtrSlot ps, const float* __restrict__ p_mem, float* __re
   const float* P = p_mem + md.p_off;
   const unsigned in_flags = ps.flags[t.mat];
   pdl_wait();
-  if (md.cpt == 4) {
+  bool done_tc = false;
+  if constexpr (R >= 16 && kThreads3 == kTcThreads) {
+    if (use_tc && md.cpt == 4 && (in_flags & kFlagInVec)) {  // tensor pipe (3 x TF32), psgd_tc.cuh
+      q_tile_tc<R>(md, t, M, P, ws, smem);
+      done_tc = true;
+    }
+  }
+  if (done_tc) {
+  } else if (md.cpt == 4) {
     if (in_flags & kFlagInVec)
       q_tile<R, 4, true, kThreads3>(md, t, M, P, ws, smem);
     else
@@ -973,32 +1070,6 @@ k_momentum_step(const VecTile* __restrict__ tiles, float* const* __restrict__ pa
 //   alternate, and a rank can only overwrite its P input after it has passed the Q barrier (and vice versa),
 //   which every peer reaches only after it finished reading.
 // =======================================================================================
-constexpr int kMaxPeers = 8;
-struct PeerArgs {
-  const float* in[kMaxPeers];   // input buffer of every rank, mapped into this process
-  unsigned* sig[kMaxPeers];     // signal pad of every rank (uint32 slots), mapped into this process
-};
-
-__device__ __forceinline__ void st_release_sys(unsigned* p, unsigned v) {
-  asm volatile("st.release.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-__device__ __forceinline__ unsigned ld_acquire_sys(const unsigned* p) {
-  unsigned v;
-  asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ float4 ld_sys4(const float* p) {
-  float4 v;
-  asm volatile("ld.relaxed.sys.global.v4.f32 {%0,%1,%2,%3}, [%4];"
-               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ float ld_sys1(const float* p) {
-  float v;
-  asm volatile("ld.relaxed.sys.global.f32 %0, [%1];" : "=f"(v) : "l"(p) : "memory");
-  return v;
-}
-
 __global__ void __launch_bounds__(kThreads)
 k_peer_allreduce(PeerArgs a, float* __restrict__ out, long long n, int rank, int world, int slot0, unsigned epoch) {
   if (blockIdx.x == 0 && (int)threadIdx.x < world) {
@@ -1035,6 +1106,19 @@ k_peer_allreduce(PeerArgs a, float* __restrict__ out, long long n, int rank, int
 }
 
 
+// Stand-alone form of the all-reduce-on-load (fallback for steps whose consumer kernel cannot take it in: direct-load
+// kernels on unaligned tensors, matrices too tall for the register-resident Gram-Schmidt): one flag barrier, then
+// out[i] = sum over ranks of in_r[i], divided by `div` from element div_from on.
+__global__ void __launch_bounds__(kThreads)
+k_peer_reduce_to_local(PeerLoad pm, float* __restrict__ out, long long n, float div, long long div_from) {
+  peer_barrier(pm, blockIdx.x == 0);
+  const long long stride = (long long)gridDim.x * kThreads;
+  for (long long i = (long long)blockIdx.x * kThreads + threadIdx.x; i < n; i += stride) {
+    const float v = peer_sum1(pm, i);
+    out[i] = (i >= div_from && div != 1.0f) ? v / div : v;
+  }
+}
+
 // ---- the same sum through the NVSwitch multicast address of the symmetric buffer ----------------------------
 // Two-shot, in place: after a flag barrier ("every rank's input is written") rank k owns the k-th slice of the
 // buffer: one multimem.ld_reduce returns the switch-side sum of all ranks' copies of an element, one multimem.st
@@ -1042,32 +1126,6 @@ k_peer_allreduce(PeerArgs a, float* __restrict__ out, long long n, int rank, int
 // result is copied from this rank's copy to `out`.  Each element is summed exactly once, so all ranks hold the
 // same bits; a rank moves n/W elements over NVLink instead of (W-1) n.  `blocks_done` is a zero-initialised word owned
 // by the call site (one per exchange buffer): the kernel leaves it at zero.
-
-__device__ __forceinline__ float4 mm_ld_reduce4(const float* mc) {
-  float4 v;
-  asm volatile("multimem.ld_reduce.relaxed.sys.global.add.v4.f32 {%0,%1,%2,%3}, [%4];"
-               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(mc) : "memory");
-  return v;
-}
-__device__ __forceinline__ void mm_st4(float* mc, float4 v) {
-  asm volatile("multimem.st.relaxed.sys.global.v4.f32 [%0], {%1,%2,%3,%4};" ::"l"(mc), "f"(v.x), "f"(v.y), "f"(v.z),
-               "f"(v.w) : "memory");
-}
-
-// all threads of the CTA return once every rank has posted `epoch` in this rank's flags[0 .. world)
-__device__ __forceinline__ void peer_flags_wait(const unsigned* flags, int world, unsigned epoch, int rank, int which) {
-  if ((int)threadIdx.x < world) {
-    const long long t0 = clock64();
-    while ((int)(ld_acquire_sys(flags + threadIdx.x) - epoch) < 0) {
-      if (clock64() - t0 > 20000000000LL) {  // ~10 s: a crashed peer must not hang the GPU
-        printf("psgd k_peer_allreduce_mc: rank %d timed out waiting for rank %d (barrier %d, epoch %u)\n", rank,
-               (int)threadIdx.x, which, epoch);
-        __trap();
-      }
-    }
-  }
-  __syncthreads();
-}
 
 __global__ void __launch_bounds__(kThreads)
 k_peer_allreduce_mc(PeerArgs a, float* __restrict__ mc, float* __restrict__ out, long long n, int rank, int world,

@@ -18,7 +18,6 @@
 
 namespace psgd {
 
-constexpr int kConsumerWarps = 8;
 constexpr int kStreamThreads = (kConsumerWarps + 1) * 32;  // + 1 producer warp
 constexpr int kMaxSlots = 8;
 constexpr int kMatCache = 256;  // matrices whose {base, q, m, r} are cached in shared memory
@@ -198,18 +197,33 @@ __device__ __forceinline__ void mbar_arrive_n(uint64_t* bar, uint32_t count) {
 __device__ __forceinline__ void mbar_arrive_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
+// Spins until the phase with the given parity has completed.  A protocol error (or a peer GPU that never answers)
+// would otherwise hang the kernel for good: after ~4 s of waiting the thread reports and traps instead.
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
-  asm volatile(
-      "{\n"
-      ".reg .pred p;\n"
-      "WAIT_%=:\n"
-      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
-      "@p bra DONE_%=;\n"
-      "bra WAIT_%=;\n"
-      "DONE_%=:\n"
-      "}\n" ::"r"(smem_u32(bar)),
-      "r"(parity)
-      : "memory");
+  const uint32_t addr = smem_u32(bar);
+  long long t0 = 0;
+  for (unsigned spins = 1;; ++spins) {
+    uint32_t done;
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(addr), "r"(parity)
+        : "memory");
+    if (done) return;
+    if ((spins & 0x3fffu) == 0) {
+      if (t0 == 0) {
+        t0 = clock64();
+      } else if (clock64() - t0 > 8000000000LL) {
+        printf("psgd: mbarrier wait timed out (CTA %d, thread %d, smem barrier 0x%x, parity %u)\n", (int)blockIdx.x,
+               (int)threadIdx.x, addr, parity);
+        __trap();
+      }
+    }
+  }
 }
 // global -> shared bulk copy (bytes % 16 == 0, both addresses 16-byte aligned), completion on `bar`
 __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
@@ -217,9 +231,6 @@ __device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t by
                    smem_u32(dst)),
                "l"(src), "r"(bytes), "r"(smem_u32(bar))
                : "memory");
-}
-__device__ __forceinline__ void consumer_sync() {  // named barrier over the consumer warps only
-  asm volatile("bar.sync 1, %0;" ::"n"(kConsumerWarps * 32) : "memory");
 }
 
 #ifndef PSGD_K1_UNROLL_R4
@@ -231,9 +242,15 @@ __device__ __forceinline__ void consumer_sync() {  // named barrier over the con
 #ifndef PSGD_ROWS1_R8
 #define PSGD_ROWS1_R8 4
 #endif
+#ifndef PSGD_ROWS1_R16
+#define PSGD_ROWS1_R16 2
+#endif
+#ifndef PSGD_ROWS4_R16
+#define PSGD_ROWS4_R16 2
+#endif
 // rows of M one consumer warp works on at a time (every Q value read from shared memory is used ROWS times)
-__host__ __device__ constexpr int rows_s1(int R) { return (R <= 2) ? 8 : (R <= 4) ? 4 : (R <= 8) ? PSGD_ROWS1_R8 : (R == 16) ? 2 : 1; }
-__host__ __device__ constexpr int rows_s4(int R) { return (R <= 8) ? 4 : (R == 16) ? 2 : 1; }
+__host__ __device__ constexpr int rows_s1(int R) { return (R <= 2) ? 8 : (R <= 4) ? 4 : (R <= 8) ? PSGD_ROWS1_R8 : (R == 16) ? PSGD_ROWS1_R16 : 1; }
+__host__ __device__ constexpr int rows_s4(int R) { return (R <= 8) ? 4 : (R == 16) ? PSGD_ROWS4_R16 : 1; }
 template <int R> struct RowsS1 { static constexpr int v = rows_s1(R); };
 template <int R> struct RowsS4 { static constexpr int v = rows_s4(R); };
 
@@ -285,6 +302,59 @@ __device__ __forceinline__ StreamSmem::MatInfo mat_info(const DevPlan& pl, const
   return mi;
 }
 
+// ---- Q all-reduce as the prologue of a streamed kernel (reducer.py:145-147 without a launch of its own) -----------
+// After the flag barrier ("every rank's Q = M^T P is written") CTA b sums the b-th slice of Q over the ranks, divides
+// by n_workers and stores the mean to the local q_mem; a grid-wide arrival count (the grid is one CTA per SM, all
+// resident) then tells every CTA that the whole of q_mem is in place, and the kernel goes on to stage Q from there as
+// it would at one worker.  One barrier across ranks, one across the grid, no copy-out, no separate divide.
+struct PeerQ {
+  PeerLoad pm;       // pm.mode == kPeerOff: no prologue
+  float* q_out;      // local q_mem (receives the mean)
+  long long n;       // elements of Q
+  float div;         // n_workers
+  unsigned gtarget;  // value *gsync reaches once every CTA of this launch has arrived (monotonic counter)
+  unsigned* gsync;
+};
+
+__device__ __forceinline__ void fence_proxy_async() {
+  asm volatile("fence.proxy.async;" ::: "memory");
+}
+
+__device__ __forceinline__ void peer_q_prologue(const PeerQ& pq) {  // all threads of the CTA
+  pdl_wait();  // this rank's Q partials are complete
+  peer_barrier(pq.pm, blockIdx.x == 0);
+  const long long n4 = (pq.n + 3) >> 2;
+  const long long per = (n4 + gridDim.x - 1) / gridDim.x;
+  const long long lo = (long long)blockIdx.x * per;
+  const long long hi = (lo + per < n4) ? lo + per : n4;
+  for (long long i = lo + threadIdx.x; i < hi; i += blockDim.x) {
+    float4 v = peer_sum4(pq.pm, 4 * i);  // the symmetric buffers are padded to whole float4s
+    v.x = v.x / pq.div; v.y = v.y / pq.div; v.z = v.z / pq.div; v.w = v.w / pq.div;
+    if (4 * i + 4 <= pq.n) {
+      *reinterpret_cast<float4*>(pq.q_out + 4 * i) = v;
+    } else {
+      const float t[4] = {v.x, v.y, v.z, v.w};
+      for (int k = 0; 4 * i + k < pq.n; ++k) pq.q_out[4 * i + k] = t[k];
+    }
+  }
+  __threadfence();
+  fence_proxy_async();  // q_mem is read next by bulk copies (async proxy), possibly of another SM
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    atomicAdd(pq.gsync, 1u);
+    const long long t0 = clock64();
+    while ((int)(ld_acquire_gpu(pq.gsync) - pq.gtarget) < 0) {
+      if (clock64() - t0 > 20000000000LL) {
+        printf("psgd: grid-wide Q arrival timed out in CTA %d (rank %d)\n", (int)blockIdx.x, pq.pm.rank);
+        __trap();
+      }
+    }
+    __threadfence();
+  }
+  __syncthreads();
+  fence_proxy_async();
+}
+
 // common prologue: barriers + matrix cache
 __device__ __forceinline__ void stream_setup(const DevPlan& pl, const PtrSlot& ps, const StreamPlan& sp,
                                              const StreamSmem& sm, const float* q_mem) {
@@ -311,6 +381,9 @@ __device__ __forceinline__ void stream_setup(const DevPlan& pl, const PtrSlot& p
 }
 
 
+// The producer: one thread takes tasks from the global counter, cuts them into units and refills slots
+// as the consumers release them.  Nothing on its per-unit path touches global memory: the task after
+// the current one is requested while the current one streams.
 // The producer: one thread takes tasks from the global counter, cuts them into units and refills slots
 // as the consumers release them.  Nothing on its per-unit path touches global memory: the task after
 // the current one is requested while the current one streams.
@@ -342,7 +415,7 @@ __device__ __forceinline__ void stream_producer(const DevPlan& pl, const PtrSlot
           mbar_arrive_expect_tx(&sm.full[slot], bytes);
           bulk_g2s(sm.ring + (size_t)slot * sp.slot_bytes, mi.q + (size_t)j0 * mi.r, bytes, &sm.full[slot]);
         } else {
-          mbar_arrive(&sm.full[slot]);
+          mbar_arrive(&sm.full[slot]);  // every use of a slot completes one phase of each of its barriers
         }
       }
       prev_mat = task.mat;
@@ -430,7 +503,7 @@ __device__ __forceinline__ void consume_q_unit(float* Qs, const float* slot, con
 template <int R, bool FUSE>
 __global__ void __launch_bounds__(kStreamThreads, 1)
 k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict__ q_mem, float* __restrict__ p_mem,
-                  float q_div) {
+                  float q_div, PeerQ pq) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   constexpr int ROWS = RowsS1<R>::v;
   constexpr int RG = (ROWS * R > 32) ? 32 / R : ROWS;  // rows per butterfly fold (at most 32 values)
@@ -439,6 +512,7 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
   const StreamSmem sm = carve(smem_raw, sp);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   stream_setup(pl, ps, sp, sm, q_mem);
+  if (pq.pm.mode != kPeerOff) peer_q_prologue(pq);  // extra power iterations at N > 1: Q still has to be summed
 
   if (warp == kConsumerWarps) {
     if (lane == 0) stream_producer<ROWS, FUSE>(pl, ps, sp, sm, q_mem);
@@ -597,12 +671,13 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
 template <int R>
 __global__ void __launch_bounds__(kStreamThreads, 1)
 k_finalize_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict__ p_mem,
-                  const float* __restrict__ q_mem, float world) {
+                  const float* __restrict__ q_mem, float world, PeerQ pq) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
   constexpr int ROWS = RowsS4<R>::v;
   const StreamSmem sm = carve(smem_raw, sp);
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   stream_setup(pl, ps, sp, sm, q_mem);
+  if (pq.pm.mode != kPeerOff) peer_q_prologue(pq);
 
   if (warp == kConsumerWarps) {
     if (lane == 0) stream_producer<ROWS>(pl, ps, sp, sm, q_mem);

@@ -95,6 +95,27 @@ class CudaPlan:
         _lib.check(self._lib.psgd_p_from_m_pack(self._h, p_mem.data_ptr(), q_mem.data_ptr(), int(fuse_add),
                                                 float(q_div), flat.data_ptr(), _stream(self.device)), self._lib)
 
+    def p_from_m_orth(self, p_mem, q_mem, flat=None, fuse_add=False, q_div=1.0):
+        """Single worker: P = M Q and its Gram-Schmidt in one call (no all-reduce sits between them); the q_from_mt
+        call that follows overlaps what is left of the orthogonalisation."""
+        _lib.check(self._lib.psgd_p_from_m_orth(self._h, p_mem.data_ptr(), q_mem.data_ptr(), int(fuse_add), float(q_div),
+                                                flat.data_ptr() if flat is not None else None, _stream(self.device)),
+                   self._lib)
+
+    # -- N > 1 inside one NVLink domain: the all-reduces ride inside these launches (peer.PeerExchange, fused modes) --
+    def p_from_m_peer(self, peer, p_mem, q_mem, fuse_add=False):
+        _lib.check(self._lib.psgd_p_from_m_peer(self._h, peer.handle, p_mem.data_ptr(), q_mem.data_ptr(), int(fuse_add),
+                                                _stream(self.device)), self._lib)
+
+    def orthogonalize_peer(self, peer, p_mem, flat_out):
+        _lib.check(self._lib.psgd_orthogonalize_peer(self._h, peer.handle, p_mem.data_ptr(),
+                                                     flat_out.data_ptr() if flat_out is not None else None,
+                                                     _stream(self.device)), self._lib)
+
+    def finalize_peer(self, peer, p_mem, q_mem, flat):
+        _lib.check(self._lib.psgd_finalize_peer(self._h, peer.handle, p_mem.data_ptr(), q_mem.data_ptr(), flat.data_ptr(),
+                                                _stream(self.device)), self._lib)
+
     def finalize_unpack(self, p_mem, q_mem, n_workers, flat):
         """finalize with the scatter of the flat buffer folded into the same launch."""
         _lib.check(self._lib.psgd_finalize_unpack(self._h, p_mem.data_ptr(), q_mem.data_ptr(), float(n_workers),

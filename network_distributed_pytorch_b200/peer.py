@@ -1,15 +1,21 @@
-"""Peer-memory exchange for the two packed all-reduces of a step (reducer.py:126,132,145) inside one NVLink domain.
+"""Peer-memory exchange for the packed all-reduces of a step (reducer.py:126,132,145) inside one NVLink domain.
 
-The input buffers of the two phases live in torch symmetric memory (every rank maps every other rank's buffer and
-signal pad); the sum itself is this package's own kernel.  Where the fabric gives the buffers a multicast mapping
-(NVSwitch), psgd_peer_allreduce_mc sums rank k's slice inside the switch (multimem.ld_reduce) and stores it into every
-rank's copy (multimem.st); otherwise psgd_peer_allreduce has each rank read all ranks' inputs and add them in rank
-order.  Either way every rank gets the same bits.  Set-up is a collective; if it fails on any rank every rank falls
-back to torch.distributed.all_reduce (NCCL).
+The buffers the P = M Q and Q = M^T P kernels write live in torch symmetric memory (every rank maps every other rank's
+buffer and signal pad).  Two families of implementation, all this package's own kernels:
 
-PSGD_PEER_ALLREDUCE: 1 / 0 force it on / off; unset, the multicast kernel is used from 8 ranks on and NCCL below
-(PSGD_PEER_MULTICAST=0 forces the pull kernel where the exchange is on).  Measured DistilBERT r=4 step on B200s:
-2 GPUs NCCL 0.280 ms, pull 0.278, multicast 0.302; 8 GPUs NCCL 0.307, pull 0.318, multicast 0.294."""
+* fused (default): no all-reduce launch at all.  The Gram-Schmidt kernel takes a flag barrier and loads its rows
+  summed over the ranks; the streamed finalize kernel (and the P = M Q kernel of a later power iteration) does the same
+  for Q in its prologue (psgd_orthogonalize_peer / psgd_finalize_peer / psgd_p_from_m_peer).  The sum is formed either
+  by the NVSwitch (``multimem.ld_reduce``, mode "multimem") or by one load per rank added in rank order (mode "pull",
+  bit-identical on all ranks by construction, needs no multicast mapping).
+* kernel: the round-1 stand-alone kernels between the phases (two-shot through the multicast mapping where the fabric
+  has one, else one-shot pull) -- kept as a comparison point and as the parity cross-check.
+
+Set-up is a collective; if it fails on any rank every rank falls back to torch.distributed.all_reduce (NCCL).
+
+PSGD_PEER_ALLREDUCE: 0 = NCCL, 1 = this module, unset = this module from 2 ranks on (inside one node).
+PSGD_PEER_MODE: pull | multimem | kernel (default: pull).
+"""
 import ctypes
 import os
 
@@ -20,10 +26,11 @@ from . import _lib
 
 _SLOT0 = 256          # first signal-pad slot used by this package (torch's own barrier uses the low slots)
 MAX_WORLD = 8
+_MODE_IDS = {"multimem": 1, "pull": 2}
 
 
 class PeerExchange:
-    def __init__(self, device, n_pf, n_q):
+    def __init__(self, device, n_pf, n_q, mode):
         import torch.distributed._symmetric_memory as symm
 
         self.device = device
@@ -40,12 +47,20 @@ class PeerExchange:
                 raise RuntimeError("unexpected symmetric memory geometry")
         self._in = [_lib.ptr_array(list(h.buffer_ptrs)) for h in self.hdl]
         self._sig = [_lib.ptr_array(list(h.signal_pad_ptrs)) for h in self.hdl]
-        # NVSwitch multicast mapping of the two buffers (0 when the fabric has none): in-switch two-shot sum
+        # NVSwitch multicast mapping of the two buffers (0 when the fabric has none)
         self._mc = [int(getattr(h, "multicast_ptr", 0) or 0) for h in self.hdl]
-        if os.environ.get("PSGD_PEER_MULTICAST", "1") != "1" or not all(self._mc):
-            self._mc = [0, 0]
-        self.multicast = bool(self._mc[0])
-        self.kind = "kernel-multicast" if self.multicast else "kernel-pull"
+        have_mc = all(self._mc) and os.environ.get("PSGD_PEER_MULTICAST", "1") == "1"
+        if mode == "multimem" and not have_mc:
+            mode = "pull"
+        self.fused = mode in _MODE_IDS
+        if self.fused:
+            self.kind = "fused-" + mode
+            self.multicast = False
+        else:
+            if not have_mc:
+                self._mc = [0, 0]
+            self.multicast = bool(self._mc[0])
+            self.kind = "kernel-multicast" if self.multicast else "kernel-pull"
         self.epoch = [0, 0]
         self._done = torch.zeros(2, dtype=torch.int32, device=device)  # per-buffer CTA completion word of the multicast kernel
         for b in self.buf:
@@ -56,16 +71,42 @@ class PeerExchange:
         for h in self.hdl:
             pad = h.get_signal_pad(self.rank, (h.signal_pad_size // 4,), torch.int32)
             pad[_SLOT0 : _SLOT0 + 2 * MAX_WORLD].zero_()
+        self._h = None
+        if self.fused:
+            handle = ctypes.c_void_p()
+            _lib.check(self._lib.psgd_peer_create(
+                self.world, self.rank, device.index, self._in[0], self._sig[0],
+                ctypes.c_void_p(self._mc[0] if mode == "multimem" else 0), self._in[1], self._sig[1],
+                ctypes.c_void_p(self._mc[1] if mode == "multimem" else 0), _SLOT0, _MODE_IDS[mode], ctypes.byref(handle)),
+                self._lib)
+            self._h = handle
         torch.cuda.synchronize(device)
         dist.barrier()
 
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            try:
+                self._lib.psgd_peer_destroy(h)
+            except Exception:
+                pass
+
     def describe(self):
-        return {"kernel-multicast": "own kernel, NVSwitch multicast (multimem), two-shot",
+        return {"fused-pull": "none as a launch: summed on load inside the Gram-Schmidt and finalize kernels (one load per rank, rank order)",
+                "fused-multimem": "none as a launch: summed on load inside the Gram-Schmidt and finalize kernels (multimem.ld_reduce in the NVSwitch)",
+                "kernel-multicast": "own kernel, NVSwitch multicast (multimem), two-shot",
                 "kernel-pull": "own kernel, peer pull"}[self.kind]
 
+    @property
+    def handle(self):
+        return self._h
+
     def allreduce(self, which, out, n, div=1.0, div_from=0):
-        """out[:n] = sum over ranks of buf[which][:n]  (which: 0 = P || flat, 1 = Q).  With the multicast kernel the
-        elements from div_from on leave as sum / div (callers check .multicast before asking for that)."""
+        """Stand-alone kernels ("kernel" mode): out[:n] = sum over ranks of buf[which][:n]  (which: 0 = P || flat,
+        1 = Q).  With the multicast kernel the elements from div_from on leave as sum / div (callers check .multicast
+        before asking for that)."""
+        if self.fused:
+            raise RuntimeError("a fused exchange has no stand-alone all-reduce")
         if div != 1.0 and not self._mc[which]:
             raise RuntimeError("the pull kernel returns plain sums")
         self.epoch[which] += 1
@@ -82,30 +123,26 @@ class PeerExchange:
                    self._lib)
 
 
-AUTO_MIN_WORLD = 8   # from this many ranks on the multicast kernel beat NCCL in the measurements
-
-
-def mode_for(world, setting):
-    """What PSGD_PEER_ALLREDUCE asks for: 'off', 'on' (either kernel) or 'multicast-only'.
-    '1' / '0' force it on / off; unset (or 'auto') turns the multicast kernel on from AUTO_MIN_WORLD ranks."""
+def enabled_for(world, setting):
+    """PSGD_PEER_ALLREDUCE: '1' / '0' force the peer exchange on / off; unset (or 'auto') turns it on from two ranks."""
     if world < 2 or world > MAX_WORLD or setting == "0":
-        return "off"
-    if setting == "1":
-        return "on"
-    return "multicast-only" if world >= AUTO_MIN_WORLD else "off"
+        return False
+    return True
 
 
 def try_setup(device, n_pf, n_q):
     """Collective.  Returns a PeerExchange on every rank, or None on every rank."""
     world = dist.get_world_size()
-    mode = mode_for(world, os.environ.get("PSGD_PEER_ALLREDUCE", "auto"))
-    if mode == "off" or device.type != "cuda" or dist.get_backend() != "nccl":
+    if not enabled_for(world, os.environ.get("PSGD_PEER_ALLREDUCE", "auto")):
         return None
+    if device.type != "cuda" or dist.get_backend() != "nccl":
+        return None
+    mode = os.environ.get("PSGD_PEER_MODE", "pull")
+    if mode not in ("pull", "multimem", "kernel"):
+        raise ValueError("PSGD_PEER_MODE must be pull, multimem or kernel")
     ex, ok = None, 1
     try:
-        ex = PeerExchange(device, n_pf, n_q)
-        if mode == "multicast-only" and not ex.multicast:
-            ok = 0  # the pull kernel loses to NCCL at this size
+        ex = PeerExchange(device, n_pf, n_q, mode)
     except Exception as exc:  # noqa: BLE001 -- any failure means "use NCCL", decided jointly below
         ok = 0
         if os.environ.get("PSGD_DEBUG"):

@@ -217,32 +217,53 @@ class PowerSGDReducer(Reducer):
                 plan.pack_vec(flat_in)
         bits_communicated += 8 * flat.nelement() * flat.element_size()
 
-        # The multicast all-reduce sums in place and can hand out means: the flat buffer and Q then arrive already
-        # divided by n_workers, and the later kernels are told a world of 1 for them (same IEEE division, same bits).
-        mean_out = px is not None and px.multicast
+        fused_px = px is not None and px.fused
+        # The stand-alone multicast all-reduce sums in place and can hand out means: the flat buffer and Q then arrive
+        # already divided by n_workers, and the later kernels are told a world of 1 for them (same IEEE division).
+        mean_out = px is not None and not px.fused and px.multicast
         late_world = 1.0 if mean_out else world
+        solo = world == 1 and hasattr(plan, "p_from_m_orth")  # no all-reduce between steps 3 and 5: one fused call
         for it in range(self.extra_power_iterations + 1):
-            # Step 3 (reducer.py:121-123) P <- M Q
-            if fold and it == 0:
-                plan.p_from_m_pack(p_in, self.q_memory, flat_in, fuse_add=fused)
-            else:
-                plan.p_from_m(p_in, self.q_memory, fuse_add=(fused and it == 0), q_div=(late_world if it > 0 else 1.0))
-            # Step 4 (reducer.py:126-128) ALL_REDUCE_MEAN(P); the divide is folded into step 5
-            if px is not None:
-                # the flat buffer travels with the first P only (a second in-place sum would count it twice)
+            if solo:
+                # Steps 3 + 5 (reducer.py:121-123, 136-137); step 4's all-reduce is skipped upstream at one worker
+                plan.p_from_m_orth(p_in, self.q_memory, flat_in if (fold and it == 0) else None,
+                                   fuse_add=(fused and it == 0))
+                bits_communicated += n_bits(self.p_memory)
+            elif fused_px:
+                # Step 3; from the second power iteration on the kernel first sums Q over the ranks (step 7 of the
+                # previous iteration) in its prologue
                 if it == 0:
-                    px.allreduce(0, self._p_and_flat, n_pf, div=(world if mean_out else 1.0), div_from=plan.p_elems)
+                    plan.p_from_m_pack(p_in, self.q_memory, flat_in, fuse_add=fused)
                 else:
-                    px.allreduce(0, self._p_and_flat, plan.p_elems)
+                    plan.p_from_m_peer(px, p_in, self.q_memory)
+                # Steps 4 + 5 (+ the flat buffer's all-reduce and mean): ALL_REDUCE_MEAN(P) happens on load inside the
+                # Gram-Schmidt launch
+                plan.orthogonalize_peer(px, self.p_memory, flat if it == 0 else None)
+                bits_communicated += n_bits(self.p_memory)
             else:
-                all_reduce(self._p_and_flat if it == 0 else self.p_memory)
-            bits_communicated += n_bits(self.p_memory)
-            # Step 5 (reducer.py:136-137) P_hat <- ORTHOGONALIZE(P / n_workers)
-            plan.orthogonalize(self.p_memory, world)
+                # Step 3 (reducer.py:121-123) P <- M Q
+                if fold and it == 0:
+                    plan.p_from_m_pack(p_in, self.q_memory, flat_in, fuse_add=fused)
+                else:
+                    plan.p_from_m(p_in, self.q_memory, fuse_add=(fused and it == 0), q_div=(late_world if it > 0 else 1.0))
+                # Step 4 (reducer.py:126-128) ALL_REDUCE_MEAN(P); the divide is folded into step 5
+                if px is not None:
+                    # the flat buffer travels with the first P only (a second in-place sum would count it twice)
+                    if it == 0:
+                        px.allreduce(0, self._p_and_flat, n_pf, div=(world if mean_out else 1.0), div_from=plan.p_elems)
+                    else:
+                        px.allreduce(0, self._p_and_flat, plan.p_elems)
+                else:
+                    all_reduce(self._p_and_flat if it == 0 else self.p_memory)
+                bits_communicated += n_bits(self.p_memory)
+                # Step 5 (reducer.py:136-137) P_hat <- ORTHOGONALIZE(P / n_workers)
+                plan.orthogonalize(self.p_memory, world)
             # Step 6 (reducer.py:140-142) Q <- M^T P_hat
             plan.q_from_mt(self.p_memory, q_in)
             # Step 7 (reducer.py:145-147) ALL_REDUCE_MEAN(Q); the divide is applied while Q is staged
-            if px is not None:
+            if fused_px:
+                pass  # summed on load by the next streamed kernel (finalize, or the next iteration's P = M Q)
+            elif px is not None:
                 px.allreduce(1, self.q_memory, plan.q_elems, div=(world if mean_out else 1.0))
             else:
                 all_reduce(self.q_memory)
@@ -250,7 +271,9 @@ class PowerSGDReducer(Reducer):
 
         # Step 8 + 9 (reducer.py:158-163) decompress and memorise the local error in one sweep
         # [For Rank 1] (reducer.py:166-168) mean + scatter ride on the same launch; q_memory becomes the mean in place
-        if fold:
+        if fused_px:
+            plan.finalize_peer(px, self.p_memory, self.q_memory, flat)
+        elif fold:
             plan.finalize_unpack(self.p_memory, self.q_memory, late_world, flat)
             if world > 1 and not mean_out:
                 plan.finish(None, self.q_memory, world)

@@ -37,12 +37,13 @@ def within_tolerance(res, tol=TOL):
 
 
 def run_pair(shapes, rank, steps=1, reuse=True, seed=714, data_seed=0, extra=0, offset_elems=0, scale_cols=False,
-             arbiter=True):
+             arbiter=True, sync_q=False):
     """Run the CUDA reducer and the CPU oracle on the same seeded inputs and the same query.
 
     Returns a list (per step) of dicts with per-tensor relative errors of grad_out / memory_out and the
     relative errors of the packed P / Q buffers.  ``offset_elems`` places every CUDA tensor that many
-    elements into a larger allocation (exercises the unaligned code paths)."""
+    elements into a larger allocation (exercises the unaligned code paths).  ``sync_q`` also hands the oracle's Q to the
+    CUDA reducer after every step, so that with ``reuse_query`` every step is a single-step comparison."""
     from network_distributed_pytorch_b200.reducer import PowerSGDReducer
 
     ensure_group()
@@ -92,6 +93,8 @@ def run_pair(shapes, rank, steps=1, reuse=True, seed=714, data_seed=0, extra=0, 
                 send_equal=all(torch.equal(a.cpu(), b) for a, b in zip(send_g, send_c))))
             for a, b in zip(mem_g, mem_c):
                 a.copy_(b)
+            if sync_q:
+                red.q_memory.copy_(orc.q_memory)
             continue
         # fp64 arbiter, single step from the same state as the fp32 runs
         out_d = [torch.zeros(s, dtype=torch.float64) for s in shapes]
@@ -114,6 +117,8 @@ def run_pair(shapes, rank, steps=1, reuse=True, seed=714, data_seed=0, extra=0, 
         # keep the two trajectories on identical inputs: feed the oracle's memory to both
         for a, b in zip(mem_g, mem_c):
             a.copy_(b)
+        if sync_q:
+            red.q_memory.copy_(orc.q_memory)
     return results
 
 

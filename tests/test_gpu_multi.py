@@ -80,26 +80,69 @@ assert rel_err(red.p_memory.cpu().numpy(), orc.p_memory.numpy()) < TOL
 assert rel_err(red.q_memory.cpu().numpy(), orc.q_memory.numpy()) < TOL
 assert max(per_tensor_rel_err(flatten(gout), flatten(o_out[rank]), shapes)) < TOL
 assert max(per_tensor_mem_err(flatten(mem), flatten(o_mem[rank]), flatten(ins[rank]), shapes)) < TOL
+# the reference-generated case at realistic sizes (tests/golden/w2_r4_medium.npz): streamed kernels, cluster Gram-Schmidt
+from tests.helpers import MediumGolden
+mg = MediumGolden()
+mine = mg.inputs(rank)
+if mine is not None:
+    red._set_random = None
+    red = PowerSGDReducer(mg.seed, dev, 0, True, mg.rank)
+    qbuf = {"buf": torch.from_numpy(mg.get(0, "qinit")).to(dev), "off": 0}
+    def fake_q(vector, red=red, st=qbuf):
+        red.rng.randint(1_000_000_000)
+        k = vector.nelement()
+        vector.data[:] = st["buf"][st["off"]:st["off"] + k].view(vector.shape)
+        st["off"] += k
+    red._set_random = fake_q
+    gin = [t.to(dev) for t in mine]
+    gout = [torch.zeros(s, device=dev) for s in mg.shapes]
+    mem = [torch.zeros(s, device=dev) for s in mg.shapes]
+    bits = red.reduce(gin, gout, mem)
+    torch.cuda.synchronize()
+    assert bits == int(mg.get(0, "bits"))
+    assert rel_err(red.p_memory.cpu().numpy(), mg.get(0, "p")) < TOL
+    assert rel_err(red.q_memory.cpu().numpy(), mg.get(0, "q")) < TOL
+    mg.check_outputs(rank, gout, mem, TOL)
+    for t in (red.p_memory, red.q_memory, torch.cat([x.reshape(-1) for x in gout])):
+        both = [torch.empty_like(t) for _ in range(2)]
+        dist.all_gather(both, t.contiguous())
+        assert torch.equal(both[0], both[1])
+    red._set_random = None
 dist.destroy_process_group()
-print("rank", rank, "ok", "peer=%s" % (red._peer is not None),
-      "multicast=%s" % bool(red._peer is not None and red._peer.multicast))
+print("rank", rank, "ok", "peer=%s" % (red._peer is not None), "kind=%s" % (red._peer.kind if red._peer is not None else "nccl"))
 '''
 
 
+MODES = {  # name -> environment
+    "fused-pull": {"PSGD_PEER_ALLREDUCE": "1", "PSGD_PEER_MODE": "pull"},
+    "fused-multimem": {"PSGD_PEER_ALLREDUCE": "1", "PSGD_PEER_MODE": "multimem"},
+    "kernel-multicast": {"PSGD_PEER_ALLREDUCE": "1", "PSGD_PEER_MODE": "kernel"},
+    "kernel-pull": {"PSGD_PEER_ALLREDUCE": "1", "PSGD_PEER_MODE": "kernel", "PSGD_PEER_MULTICAST": "0"},
+    "nccl": {"PSGD_PEER_ALLREDUCE": "0"},
+    "default": {},
+}
+
+
 @pytest.mark.skipif(torch.cuda.device_count() < 2, reason="needs two GPUs")
-# own all-reduce through the NVSwitch multicast mapping / own one-shot peer pull / torch.distributed (NCCL)
-@pytest.mark.parametrize("peer", ["multicast", "pull", "nccl"])
+# the all-reduces taken into the kernels (two ways of summing), the stand-alone kernels, torch.distributed (NCCL), and
+# whatever the package picks when nothing is set
+@pytest.mark.parametrize("peer", list(MODES))
 def test_two_gpus_match_two_rank_reference(tmp_path, peer):
     script = tmp_path / "worker.py"
     script.write_text(WORKER)
-    env = dict(os.environ, PSGD_ROOT=ROOT, PSGD_PEER_ALLREDUCE="0" if peer == "nccl" else "1",
-               PSGD_PEER_MULTICAST="1" if peer == "multicast" else "0", PSGD_DEBUG="1")
+    env = dict(os.environ, PSGD_ROOT=ROOT, PSGD_DEBUG="1")
+    for k in ("PSGD_PEER_ALLREDUCE", "PSGD_PEER_MODE", "PSGD_PEER_MULTICAST"):
+        env.pop(k, None)
+    env.update(MODES[peer])
     out = subprocess.run([sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node=2",
                           "--master-addr", "127.0.0.1", "--master-port", "29533", str(script)],
-                         env=env, capture_output=True, text=True, timeout=300)
+                         env=env, capture_output=True, text=True, timeout=420)
     assert out.returncode == 0, out.stdout[-3000:] + out.stderr[-3000:]
-    assert out.stdout.count("ok") == 2
-    if peer != "nccl":
+    assert out.stdout.count(" ok ") == 2, out.stdout[-2000:]
+    print(out.stdout[-400:])
+    if peer == "nccl":
+        assert "kind=nccl" in out.stdout
+    elif peer != "default":
         assert "peer=True" in out.stdout, out.stdout[-2000:]
-    if peer == "multicast" and "multicast=True" not in out.stdout:
-        pytest.skip("no multicast mapping on this fabric: the pull kernel ran instead")
+        if ("kind=" + peer) not in out.stdout:
+            pytest.skip("no multicast mapping on this fabric: the pull form ran instead")

@@ -262,18 +262,19 @@ def test_medium_reference_case_world2_emulated_on_one_gpu():
 def test_back_to_back_launches_with_co_resident_ctas(monkeypatch):
     """Two power iterations at world 1 chain K1 -> K2 -> K3 -> K1 with programmatic dependent launch and nothing in
     between; a small grid and small ring slots let CTAs of consecutive streamed launches share an SM, the situation in
-    which two launches must not share a task counter.  Many steps, every one checked against the oracle.  A task
-    computed with the wrong launch's Q is an O(1) error in P; the bound here is 1e-4 instead of 1e-5 only because each
-    run reuses its own Q across steps and repeated power iterations on flat-spectrum random matrices amplify the
-    1e-7 differences between two fp32 implementations ('Tolerance')."""
+    which two launches must not share a task counter.  Many steps, every one a single-step comparison with the oracle
+    (memory and Q are re-synchronised after each step: repeated power iterations on flat-spectrum random matrices amplify
+    the 1e-7 differences between two fp32 implementations, SURVEY.md section 7 'Tolerance')."""
+    from tests.gpu_common import within_tolerance
+
     from tests.gpu_common import run_pair
 
     monkeypatch.setenv("PSGD_STREAM_GRID", "24")
     monkeypatch.setenv("PSGD_SLOT_BYTES", "8192")
     shapes = [(256, 512), (512,), (512, 256), (3,), (1024, 64), (64, 1024), (96, 128), (128,)]
     for extra in (1, 2):
-        for res in run_pair(shapes, 4, steps=6, extra=extra):
-            assert max(res["out"]) < 1e-4 and max(res["mem"]) < 1e-4 and res["p"] < 1e-4 and res["q"] < 1e-4, (extra, res)
+        for res in run_pair(shapes, 4, steps=6, extra=extra, sync_q=True):
+            assert within_tolerance(res) == [] and res["p"] < TOL and res["q"] < TOL, (extra, res)
 
 
 @pytest.mark.parametrize("rank", [4, 8])

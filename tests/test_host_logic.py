@@ -148,10 +148,9 @@ def test_module_helpers():
 
 
 def test_peer_allreduce_selection():
-    """PSGD_PEER_ALLREDUCE: forced on / off, otherwise the multicast kernel from 8 ranks on (peer.py)."""
+    """PSGD_PEER_ALLREDUCE: forced on / off, otherwise on from two ranks (inside one node, up to MAX_WORLD) (peer.py)."""
     from network_distributed_pytorch_b200 import peer
 
-    assert peer.mode_for(1, "auto") == "off" and peer.mode_for(2, "auto") == "off" and peer.mode_for(4, "auto") == "off"
-    assert peer.mode_for(8, "auto") == "multicast-only"
-    assert peer.mode_for(8, "0") == "off" and peer.mode_for(2, "1") == "on" and peer.mode_for(8, "1") == "on"
-    assert peer.mode_for(peer.MAX_WORLD + 1, "1") == "off"
+    assert not peer.enabled_for(1, "auto") and peer.enabled_for(2, "auto") and peer.enabled_for(8, "auto")
+    assert not peer.enabled_for(8, "0") and peer.enabled_for(2, "1")
+    assert not peer.enabled_for(peer.MAX_WORLD + 1, "1")
