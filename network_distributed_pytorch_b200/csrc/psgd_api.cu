@@ -1293,7 +1293,8 @@ int psgd_peer_create(int world, int rank, int device, const void* const* pf_bufs
     }
     pm.mc = (const float*)(w == 0 ? pf_multicast : q_multicast);
     if ((uintptr_t)pm.mc & 15) { delete h; return fail("psgd_peer_create: multicast address must be 16-byte aligned"); }
-    pm.rank = rank; pm.world = world; pm.slot0 = slot0; pm.mode = mode; pm.epoch = 0; pm.pad_ = 0;
+    pm.rank = rank; pm.world = world; pm.slot0 = slot0; pm.mode = mode; pm.epoch = 0;
+    pm.light = env_ll("PSGD_PEER_LIGHT", 0) != 0 ? 1 : 0;
   }
   if (cudaSetDevice(device) != cudaSuccess || cudaMalloc((void**)&h->d_gsync, sizeof(unsigned)) != cudaSuccess ||
       cudaMemset(h->d_gsync, 0, sizeof(unsigned)) != cudaSuccess) {

@@ -172,7 +172,7 @@ struct PeerLoad {
   const float* mc;
   int rank, world, slot0, mode;
   unsigned epoch;
-  int pad_;
+  int light;  // flag protocol: 0 = st.release.sys / ld.acquire.sys, 1 = device-scope fences around relaxed system-scope accesses
 };
 enum { kPeerOff = 0, kPeerMultimem = 1, kPeerPull = 2 };
 
@@ -180,8 +180,32 @@ enum { kPeerOff = 0, kPeerMultimem = 1, kPeerPull = 2 };
 // waits until all ranks have said so.  All threads of the CTA must call it (it ends in __syncthreads()).
 __device__ __forceinline__ void peer_barrier(const PeerLoad& pm, bool announce) {
   if (announce && (int)threadIdx.x < pm.world) {
-    __threadfence_system();
-    st_release_sys(pm.sig[threadIdx.x] + pm.slot0 + pm.rank, pm.epoch);
+    // everything this thread has observed (the finished grids before its dependency wait) is ordered before the flag
+    if (pm.light) {
+      // peers read this GPU's memory through this GPU's L2, so a device-scope fence orders the data before the flag
+      __threadfence();
+      asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(pm.sig[threadIdx.x] + pm.slot0 + pm.rank), "r"(pm.epoch) : "memory");
+    } else {
+      st_release_sys(pm.sig[threadIdx.x] + pm.slot0 + pm.rank, pm.epoch);
+    }
+  }
+  if (pm.light) {
+    if ((int)threadIdx.x < pm.world) {
+      const unsigned* f = pm.sig[pm.rank] + pm.slot0 + threadIdx.x;
+      const long long t0 = clock64();
+      for (;;) {
+        unsigned v;
+        asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(f) : "memory");
+        if ((int)(v - pm.epoch) >= 0) break;
+        if (clock64() - t0 > 20000000000LL) {
+          printf("psgd peer barrier: rank %d timed out waiting for rank %d (epoch %u)\n", pm.rank, (int)threadIdx.x, pm.epoch);
+          __trap();
+        }
+      }
+      __threadfence();
+    }
+    __syncthreads();
+    return;
   }
   peer_flags_wait(pm.sig[pm.rank] + pm.slot0, pm.world, pm.epoch, pm.rank, 0);
 }

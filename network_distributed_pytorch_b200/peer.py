@@ -14,7 +14,10 @@ buffer and signal pad).  Two families of implementation, all this package's own 
 Set-up is a collective; if it fails on any rank every rank falls back to torch.distributed.all_reduce (NCCL).
 
 PSGD_PEER_ALLREDUCE: 0 = NCCL, 1 = this module, unset = this module from 2 ranks on (inside one node).
-PSGD_PEER_MODE: pull | multimem | kernel (default: pull).
+PSGD_PEER_MODE: pull | multimem | kernel; unset: multimem where the fabric gives the buffers a multicast mapping, else
+pull.  Measured DistilBERT r=4 step on B200s (profiles/r02_allreduce_modes.md): one GPU 0.237 ms; two GPUs fused-multimem
+0.270, fused-pull 0.272, NCCL 0.274, stand-alone kernels 0.290; eight GPUs fused-multimem 0.291, stand-alone kernels
+0.294, NCCL 0.308, fused-pull 0.328 (reads (W-1) x the message).  multimem sums came out bit-identical on all eight ranks.
 """
 import ctypes
 import os
@@ -50,6 +53,8 @@ class PeerExchange:
         # NVSwitch multicast mapping of the two buffers (0 when the fabric has none)
         self._mc = [int(getattr(h, "multicast_ptr", 0) or 0) for h in self.hdl]
         have_mc = all(self._mc) and os.environ.get("PSGD_PEER_MULTICAST", "1") == "1"
+        if mode == "auto":
+            mode = "multimem" if have_mc else "pull"
         if mode == "multimem" and not have_mc:
             mode = "pull"
         self.fused = mode in _MODE_IDS
@@ -137,9 +142,9 @@ def try_setup(device, n_pf, n_q):
         return None
     if device.type != "cuda" or dist.get_backend() != "nccl":
         return None
-    mode = os.environ.get("PSGD_PEER_MODE", "pull")
-    if mode not in ("pull", "multimem", "kernel"):
-        raise ValueError("PSGD_PEER_MODE must be pull, multimem or kernel")
+    mode = os.environ.get("PSGD_PEER_MODE", "auto")
+    if mode not in ("auto", "pull", "multimem", "kernel"):
+        raise ValueError("PSGD_PEER_MODE must be auto, pull, multimem or kernel")
     ex, ok = None, 1
     try:
         ex = PeerExchange(device, n_pf, n_q, mode)
