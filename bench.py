@@ -580,6 +580,7 @@ def run_b200(args):
         modes = [("auto (the mode the timed region uses)", {})]
         if world == 2:  # cheap at two ranks: every all-reduce implementation the package has
             modes += [("nccl", {"PSGD_PEER_ALLREDUCE": "0"}),
+                      ("fused-push", {"PSGD_PEER_ALLREDUCE": "1", "PSGD_PEER_MODE": "push"}),
                       ("fused-multimem", {"PSGD_PEER_ALLREDUCE": "1", "PSGD_PEER_MODE": "multimem"}),
                       ("fused-pull", {"PSGD_PEER_ALLREDUCE": "1", "PSGD_PEER_MODE": "pull"}),
                       ("kernel-multicast", {"PSGD_PEER_ALLREDUCE": "1", "PSGD_PEER_MODE": "kernel"})]

@@ -214,6 +214,22 @@ int psgd_finalize_peer(psgd_plan* plan, psgd_peer* peer, const float* p_mem, flo
  * pf_bufs).  q_mem: local buffer receiving mean(Q). */
 int psgd_p_from_m_peer(psgd_plan* plan, psgd_peer* peer, float* p_mem, float* q_mem, int fuse_add, psgd_stream stream);
 
+/* Push form of the same idea (needs the NVSwitch multicast mapping): every rank owns a RECEIVE buffer with one slot per
+ * source rank (slot stride in floats, a multiple of 4; rx_*_local = this rank's buffer, rx_*_multicast = the multicast
+ * address of the same symmetric allocation).  The producing kernels store their results with multimem.st into slot
+ * [rank] of every rank's buffer while they run (psgd_p_from_m_push, psgd_q_from_mt_push), so that after the flag barrier
+ * psgd_orthogonalize_peer / psgd_finalize_peer / the Q prologue only add up W LOCAL slots, in slot order (bit-identical
+ * on all ranks by construction): no load crosses NVLink on the critical path. */
+int psgd_peer_create_push(int world, int rank, int device, void* rx_pf_local, void* rx_pf_multicast, int64_t pf_stride,
+                          void* const* pf_signals, void* rx_q_local, void* rx_q_multicast, int64_t q_stride,
+                          void* const* q_signals, int slot0, psgd_peer** out);
+/* K1 (reducer.py:121-123; with_flat: + the flat gather of :131) with its output pushed to every rank.  reduce_q_first:
+ * a later power iteration, Q is summed over the ranks in the kernel's prologue first (as psgd_p_from_m_peer). */
+int psgd_p_from_m_push(psgd_plan* plan, psgd_peer* peer, float* q_mem, int fuse_add, int with_flat, int reduce_q_first,
+                       psgd_stream stream);
+/* K3 (reducer.py:140-142) with its output pushed to every rank. */
+int psgd_q_from_mt_push(psgd_plan* plan, psgd_peer* peer, const float* p_mem, void* workspace, psgd_stream stream);
+
 /* In-place modified Gram-Schmidt of one n x r row-major matrix: the module-level
  * orthogonalize(matrix) of reducer.py:180-191. */
 int psgd_orthogonalize_one(float* mat, int64_t n, int r, int device, psgd_stream stream);

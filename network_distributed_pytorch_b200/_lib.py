@@ -59,6 +59,10 @@ SIGNATURES = {
                                               ctypes.c_uint32, ctypes.c_float, ctypes.c_int64, vp, ctypes.c_int, vp]),
     "psgd_peer_create": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, vp, vp, vp, vp, vp, vp, ctypes.c_int,
                                         ctypes.c_int, ctypes.POINTER(vp)]),
+    "psgd_peer_create_push": (ctypes.c_int, [ctypes.c_int, ctypes.c_int, ctypes.c_int, vp, vp, ctypes.c_int64, vp, vp, vp,
+                                             ctypes.c_int64, vp, ctypes.c_int, ctypes.POINTER(vp)]),
+    "psgd_p_from_m_push": (ctypes.c_int, [vp, vp, vp, ctypes.c_int, ctypes.c_int, ctypes.c_int, vp]),
+    "psgd_q_from_mt_push": (ctypes.c_int, [vp, vp, vp, vp, vp]),
     "psgd_peer_destroy": (ctypes.c_int, [vp]),
     "psgd_orthogonalize_peer": (ctypes.c_int, [vp, vp, vp, vp, vp]),
     "psgd_finalize_peer": (ctypes.c_int, [vp, vp, vp, vp, vp, vp]),

@@ -166,6 +166,9 @@ struct psgd_peer {
   unsigned epoch_pf = 0, epoch_q = 0;
   unsigned* d_gsync = nullptr;  // grid-wide arrival counter of the Q prologue (monotonic)
   unsigned gseq = 0;
+  // push mode (kPeerSlots): receive buffers with one slot per source rank, as ordinary and as multicast addresses
+  float *rx_pf_local = nullptr, *rx_pf_mc = nullptr, *rx_q_local = nullptr, *rx_q_mc = nullptr;
+  long long stride_pf = 0, stride_q = 0;
 };
 
 namespace {
@@ -914,7 +917,7 @@ int psgd_pack_vec(psgd_plan* p, float* flat, psgd_stream stream) {
   }
 
 static int p_from_m_impl(psgd_plan* p, float* p_mem, const float* q_mem, int fuse_add, float q_div, float* flat,
-                         psgd_stream stream, psgd_peer* peer = nullptr);
+                         psgd_stream stream, psgd_peer* peer = nullptr, bool out_mc = false);
 static PeerQ peer_q_args(psgd_plan* p, psgd_peer* peer, float* q_mem);
 static int peer_reduce_standalone(psgd_peer* peer, int which, float* out, long long n, float div, long long div_from,
                                   cudaStream_t s);
@@ -941,7 +944,7 @@ int psgd_p_from_m_pack(psgd_plan* p, float* p_mem, const float* q_mem, int fuse_
 }
 
 static int p_from_m_impl(psgd_plan* p, float* p_mem, const float* q_mem, int fuse_add, float q_div, float* flat,
-                         psgd_stream stream, psgd_peer* peer) {
+                         psgd_stream stream, psgd_peer* peer, bool out_mc) {
   if (need_device(p) || need_ptrs(p)) return 1;
   const bool tc1 = p->tc && (p->tc_mask & 1) && (fuse_add ? p->tcf_now : p->tc_now);
   const bool fold = flat && p->v_total && !p->tiles1.empty() && !tc1 && (fuse_add ? p->stream1f_now : p->stream1_now);
@@ -1001,7 +1004,7 @@ static int p_from_m_impl(psgd_plan* p, float* p_mem, const float* q_mem, int fus
   if (fuse_add ? p->stream1f_now : p->stream1_now) {
     StreamPlan sp{p->d_tasks1, p->d_counters + 2 * (p->seq1++ % kCtrRing), (int)p->tasks1.size(), p->ring_slot_bytes1, p->ring_slots1, p->q_bytes, p->d_dbg,
                   p->d_vtiles, flat, fold ? (int)p->vtiles.size() : 0, fold ? (fuse_add ? 2 : 1) : 0, 1.0f,
-                  p->d_direct_ids, p->d_direct_row_pre, (int)p->direct_ids.size(), p->split_max_sub};
+                  p->d_direct_ids, p->d_direct_row_pre, (int)p->direct_ids.size(), p->split_max_sub, out_mc ? 1 : 0};
     // peer: Q is summed over the ranks first, in the kernel's prologue when its grid is co-resident (one CTA per SM)
     if (peer && p->stream_grid > p->sm_count) {
       if (peer_reduce_standalone(peer, 1, const_cast<float*>(q_mem), p->q_total, (float)peer->world, 0, s)) return 1;
@@ -1104,7 +1107,16 @@ static int orth_impl(psgd_plan* p, float* p_mem, float n_workers, psgd_stream st
   return 0;
 }
 
+static int q_from_mt_impl(psgd_plan* p, const float* p_mem, float* q_mem, void* workspace, psgd_stream stream, bool q_mc);
+
 int psgd_q_from_mt(psgd_plan* p, const float* p_mem, float* q_mem, void* workspace, psgd_stream stream) {
+  return q_from_mt_impl(p, p_mem, q_mem, workspace, stream, false);
+}
+
+static bool k3_folds(const psgd_plan* p) { return p->d_ctr3 && env_ll("PSGD_K3_FOLD", 1) != 0; }
+
+// q_mc: q_mem is a multicast address (only with the folded second stage, whose stores then go to every rank)
+static int q_from_mt_impl(psgd_plan* p, const float* p_mem, float* q_mem, void* workspace, psgd_stream stream, bool q_mc) {
   if (need_device(p) || need_ptrs(p)) return 1;
   if (p->tiles3.empty()) return 0;
   if (!p_mem || !q_mem || !workspace) return fail("psgd_q_from_mt: null p_mem/q_mem/workspace");
@@ -1113,13 +1125,14 @@ int psgd_q_from_mt(psgd_plan* p, const float* p_mem, float* q_mem, void* workspa
   cudaStream_t s = (cudaStream_t)stream;
   const DevPlan dp = dev_plan(p);
   float* ws = (float*)workspace;
-  const bool fold = p->d_ctr3 && env_ll("PSGD_K3_FOLD", 1) != 0;
+  const bool fold = k3_folds(p);
+  if (q_mc && !fold) return fail("psgd_q_from_mt: multicast output needs the folded second stage");
   {
     PhaseScope ts(p, PSGD_PHASE_Q_FROM_MT, s);
     const unsigned grid = (unsigned)p->tiles3.size();
     DISPATCH_R(p->R, {
       if (set_smem(k_q_from_mt<RR>, p->smem3)) return 1;
-      CU(launch_ex(k_q_from_mt<RR>, dim3(grid), dim3(kThreads3), p->smem3, s, 1, p->pdl, dp, p->slot, p_mem, (float*)ws, q_mem, fold ? p->d_ctr3 : (int*)nullptr, (p->tc && (p->tc_mask & 2) && p->tc_now) ? 1 : 0));
+      CU(launch_ex(k_q_from_mt<RR>, dim3(grid), dim3(kThreads3), p->smem3, s, 1, p->pdl, dp, p->slot, p_mem, (float*)ws, q_mem, fold ? p->d_ctr3 : (int*)nullptr, (p->tc && (p->tc_mask & 2) && p->tc_now) ? 1 : 0, q_mc ? 1 : 0));
     });
     if (check_launch("k_q_from_mt")) return 1;
   }
@@ -1190,7 +1203,7 @@ static int finalize_impl(psgd_plan* p, const float* p_mem, const float* q_mem, f
   if (p->stream4_now) {
     StreamPlan sp{p->d_tasks4, p->d_counters + 2 * kCtrRing + 2 * (p->seq4++ % kCtrRing), (int)p->tasks4.size(), p->ring_slot_bytes, p->ring_slots, p->q_bytes, nullptr,
                   p->d_vtiles, const_cast<float*>(flat), fold ? (int)p->vtiles.size() : 0, fold ? 3 : 0, n_workers,
-                  p->d_direct_ids, p->d_direct_row_pre, (int)p->direct_ids.size(), 0};
+                  p->d_direct_ids, p->d_direct_row_pre, (int)p->direct_ids.size(), 0, 0};
     if (peer && p->stream_grid > p->sm_count) {
       if (peer_reduce_standalone(peer, 1, const_cast<float*>(q_mem), p->q_total, (float)peer->world, 0, s)) return 1;
       peer = nullptr;
@@ -1239,6 +1252,10 @@ int psgd_finish(psgd_plan* p, const float* flat, float* q_mem, float n_workers, 
 static PeerLoad peer_load(psgd_peer* peer, int which) {
   PeerLoad pm = which == 0 ? peer->pf : peer->q;
   pm.epoch = which == 0 ? ++peer->epoch_pf : ++peer->epoch_q;
+  if (peer->mode == kPeerSlots) {  // everything was pushed into this rank's receive buffer: W local slots
+    pm.in[0] = which == 0 ? peer->rx_pf_local : peer->rx_q_local;
+    pm.stride = which == 0 ? peer->stride_pf : peer->stride_q;
+  }
   return pm;
 }
 
@@ -1292,6 +1309,7 @@ int psgd_peer_create(int world, int rank, int device, const void* const* pf_bufs
       pm.sig[r] = (unsigned*)sigs[r];
     }
     pm.mc = (const float*)(w == 0 ? pf_multicast : q_multicast);
+    pm.stride = 0;
     if ((uintptr_t)pm.mc & 15) { delete h; return fail("psgd_peer_create: multicast address must be 16-byte aligned"); }
     pm.rank = rank; pm.world = world; pm.slot0 = slot0; pm.mode = mode; pm.epoch = 0;
     pm.light = env_ll("PSGD_PEER_LIGHT", 0) != 0 ? 1 : 0;
@@ -1303,6 +1321,85 @@ int psgd_peer_create(int world, int rank, int device, const void* const* pf_bufs
   }
   *out = h;
   return 0;
+}
+
+int psgd_peer_create_push(int world, int rank, int device, void* rx_pf_local, void* rx_pf_multicast, int64_t pf_stride,
+                          void* const* pf_signals, void* rx_q_local, void* rx_q_multicast, int64_t q_stride,
+                          void* const* q_signals, int slot0, psgd_peer** out) {
+  if (!out) return fail("out is null");
+  *out = nullptr;
+  if (world < 2 || world > kMaxPeers) return fail("psgd_peer_create_push: world size %d not in 2..%d", world, kMaxPeers);
+  if (rank < 0 || rank >= world) return fail("psgd_peer_create_push: bad rank");
+  if (device < 0) return fail("psgd_peer_create_push: needs a CUDA device");
+  if (!rx_pf_local || !rx_pf_multicast || !rx_q_local || !rx_q_multicast || !pf_signals || !q_signals)
+    return fail("psgd_peer_create_push: null pointer (push mode needs the multicast mapping of both receive buffers)");
+  if (pf_stride <= 0 || q_stride <= 0 || (pf_stride & 3) || (q_stride & 3)) return fail("psgd_peer_create_push: slot strides must be positive multiples of 4 floats");
+  if (((uintptr_t)rx_pf_local | (uintptr_t)rx_pf_multicast | (uintptr_t)rx_q_local | (uintptr_t)rx_q_multicast) & 15)
+    return fail("psgd_peer_create_push: buffers must be 16-byte aligned");
+  if (slot0 < 0) return fail("psgd_peer_create_push: bad signal slot");
+  psgd_peer* h = new psgd_peer();
+  h->device = device; h->world = world; h->rank = rank; h->mode = kPeerSlots;
+  h->rx_pf_local = (float*)rx_pf_local; h->rx_pf_mc = (float*)rx_pf_multicast; h->stride_pf = pf_stride;
+  h->rx_q_local = (float*)rx_q_local; h->rx_q_mc = (float*)rx_q_multicast; h->stride_q = q_stride;
+  for (int w = 0; w < 2; ++w) {
+    PeerLoad& pm = w == 0 ? h->pf : h->q;
+    void* const* sigs = w == 0 ? pf_signals : q_signals;
+    for (int r = 0; r < world; ++r) {
+      if (!sigs[r]) { delete h; return fail("psgd_peer_create_push: rank %d has a null signal pad", r); }
+      pm.in[r] = nullptr;
+      pm.sig[r] = (unsigned*)sigs[r];
+    }
+    pm.mc = nullptr; pm.stride = 0;
+    pm.rank = rank; pm.world = world; pm.slot0 = slot0; pm.mode = kPeerSlots; pm.epoch = 0;
+    pm.light = env_ll("PSGD_PEER_LIGHT", 0) != 0 ? 1 : 0;
+  }
+  if (cudaSetDevice(device) != cudaSuccess || cudaMalloc((void**)&h->d_gsync, sizeof(unsigned)) != cudaSuccess ||
+      cudaMemset(h->d_gsync, 0, sizeof(unsigned)) != cudaSuccess) {
+    delete h;
+    return fail("psgd_peer_create_push: device set-up failed");
+  }
+  *out = h;
+  return 0;
+}
+
+static int push_to_all(const float* local, float* mc, long long n, cudaStream_t s) {
+  if (n <= 0) return 0;
+  const unsigned grid = (unsigned)std::min<long long>(148, std::max<long long>(1, (n / 4 + kThreads - 1) / kThreads));
+  k_push_to_all<<<grid, kThreads, 0, s>>>(local, mc, n);
+  return check_launch("k_push_to_all");
+}
+
+int psgd_p_from_m_push(psgd_plan* p, psgd_peer* peer, float* q_mem, int fuse_add, int with_flat, int reduce_q_first,
+                       psgd_stream stream) {
+  if (!peer || peer->mode != kPeerSlots) return fail("psgd_p_from_m_push: needs a push-mode peer handle");
+  if (need_device(p) || need_ptrs(p)) return 1;
+  if (peer->device != p->device) return fail("psgd_p_from_m_push: plan and peer handle are on different devices");
+  if (p->p_total + p->v_total > peer->stride_pf) return fail("psgd_p_from_m_push: receive slot too small for P || flat");
+  if (with_flat && fuse_add && !p->have_vge) return fail("psgd_p_from_m_push: fuse_add needs psgd_set_ptrs_fused");
+  cudaStream_t s = (cudaStream_t)stream;
+  float* loc = peer->rx_pf_local + (long long)peer->rank * peer->stride_pf;
+  float* mcp = peer->rx_pf_mc + (long long)peer->rank * peer->stride_pf;
+  const bool want_flat = with_flat && p->v_total > 0;
+  const bool tc1 = p->tc && (p->tc_mask & 1) && (fuse_add ? p->tcf_now : p->tc_now);
+  // The streamed kernel can store straight through the multicast address when it is the only producer; otherwise
+  // the results are written to this rank's own slot and pushed by one small extra launch.
+  const bool direct = !tc1 && (fuse_add ? p->stream1f_now : p->stream1_now) && p->tiles1_fb.empty() && !p->tiles1.empty();
+  psgd_peer* pq = reduce_q_first ? peer : nullptr;
+  if (direct) return p_from_m_impl(p, mcp, q_mem, fuse_add, 1.0f, want_flat ? mcp + p->p_total : nullptr, stream, pq, true);
+  if (p_from_m_impl(p, loc, q_mem, fuse_add, 1.0f, want_flat ? loc + p->p_total : nullptr, stream, pq, false)) return 1;
+  return push_to_all(loc, mcp, p->p_total + (want_flat ? p->v_total : 0), s);
+}
+
+int psgd_q_from_mt_push(psgd_plan* p, psgd_peer* peer, const float* p_mem, void* workspace, psgd_stream stream) {
+  if (!peer || peer->mode != kPeerSlots) return fail("psgd_q_from_mt_push: needs a push-mode peer handle");
+  if (need_device(p) || need_ptrs(p)) return 1;
+  if (peer->device != p->device) return fail("psgd_q_from_mt_push: plan and peer handle are on different devices");
+  if (p->q_total > peer->stride_q) return fail("psgd_q_from_mt_push: receive slot too small for Q");
+  float* loc = peer->rx_q_local + (long long)peer->rank * peer->stride_q;
+  float* mcq = peer->rx_q_mc + (long long)peer->rank * peer->stride_q;
+  if (k3_folds(p)) return q_from_mt_impl(p, p_mem, mcq, workspace, stream, true);
+  if (q_from_mt_impl(p, p_mem, loc, workspace, stream, false)) return 1;
+  return push_to_all(loc, mcq, p->q_total, (cudaStream_t)stream);
 }
 
 int psgd_peer_destroy(psgd_peer* h) {

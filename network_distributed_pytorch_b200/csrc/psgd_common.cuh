@@ -155,6 +155,14 @@ __device__ __forceinline__ void peer_flags_wait(const unsigned* flags, int world
   __syncthreads();
 }
 
+__device__ __forceinline__ void mm_st1(float* mc, float v) {
+  asm volatile("multimem.st.relaxed.sys.global.f32 [%0], %1;" ::"l"(mc), "f"(v) : "memory");
+}
+// A result element goes either to ordinary memory or, through a multicast address, into the same place of every
+// rank's receive buffer at once ("push": the all-reduce's transfer happens while the producing kernel still runs).
+__device__ __forceinline__ void st_out(float* p, float v, bool mc) {
+  if (mc) mm_st1(p, v); else *p = v;
+}
 __device__ __forceinline__ float mm_ld_reduce1(const float* mc) {
   float v;
   asm volatile("multimem.ld_reduce.relaxed.sys.global.add.f32 %0, [%1];" : "=f"(v) : "l"(mc) : "memory");
@@ -167,14 +175,17 @@ __device__ __forceinline__ float mm_ld_reduce1(const float* mc) {
 // one load per rank, added in rank order (bit-identical on every rank by construction, needs no multicast mapping).
 // Peer data is only ever touched with plain / multimem loads and stores.
 struct PeerLoad {
-  const float* in[kMaxPeers];
+  const float* in[kMaxPeers];  // modes 1, 2: rank r's copy of the buffer; mode 3: in[0] = this rank's receive buffer
   unsigned* sig[kMaxPeers];
   const float* mc;
+  long long stride;            // mode 3: elements between the slots of the receive buffer
   int rank, world, slot0, mode;
   unsigned epoch;
   int light;  // flag protocol: 0 = st.release.sys / ld.acquire.sys, 1 = device-scope fences around relaxed system-scope accesses
 };
-enum { kPeerOff = 0, kPeerMultimem = 1, kPeerPull = 2 };
+// mode 3 ("push"): every rank has ALREADY written its contribution into slot [rank] of every rank's receive buffer
+// (multimem.st from the producing kernel), so after the flag barrier the sum is W local loads in slot order.
+enum { kPeerOff = 0, kPeerMultimem = 1, kPeerPull = 2, kPeerSlots = 3 };
 
 // "This rank's input is complete" to every peer (one CTA does it, after its own dependency wait), then every CTA
 // waits until all ranks have said so.  All threads of the CTA must call it (it ends in __syncthreads()).
@@ -211,6 +222,14 @@ __device__ __forceinline__ void peer_barrier(const PeerLoad& pm, bool announce) 
 }
 __device__ __forceinline__ float4 peer_sum4(const PeerLoad& pm, long long e) {  // e % 4 == 0, 16-byte aligned buffers
   if (pm.mode == kPeerMultimem) return mm_ld_reduce4(pm.mc + e);
+  if (pm.mode == kPeerSlots) {
+    float4 s = __ldcg(reinterpret_cast<const float4*>(pm.in[0] + e));
+    for (int r = 1; r < pm.world; ++r) {
+      const float4 v = __ldcg(reinterpret_cast<const float4*>(pm.in[0] + (long long)r * pm.stride + e));
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    return s;
+  }
   float4 s = ld_sys4(pm.in[0] + e);
   for (int r = 1; r < pm.world; ++r) {
     const float4 v = ld_sys4(pm.in[r] + e);
@@ -220,6 +239,11 @@ __device__ __forceinline__ float4 peer_sum4(const PeerLoad& pm, long long e) {  
 }
 __device__ __forceinline__ float peer_sum1(const PeerLoad& pm, long long e) {
   if (pm.mode == kPeerMultimem) return mm_ld_reduce1(pm.mc + e);
+  if (pm.mode == kPeerSlots) {
+    float s = __ldcg(pm.in[0] + e);
+    for (int r = 1; r < pm.world; ++r) s += __ldcg(pm.in[0] + (long long)r * pm.stride + e);
+    return s;
+  }
   float s = ld_sys1(pm.in[0] + e);
   for (int r = 1; r < pm.world; ++r) s += ld_sys1(pm.in[r] + e);
   return s;

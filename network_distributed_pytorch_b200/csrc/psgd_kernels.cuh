@@ -741,7 +741,7 @@ __device__ __forceinline__ void q_tile(const MatDesc& md, const ColTile& t, cons
 template <int R>
 __global__ void __launch_bounds__(kThreads3, (R <= 8) ? kMinBlocks3 : (R == 16) ? 2 : 1)
 k_q_from_mt(DevPlan pl, PtrSlot ps, const float* __restrict__ p_mem, float* __restrict__ ws, float* __restrict__ q_mem,
-            int* __restrict__ done, int use_tc) {
+            int* __restrict__ done, int use_tc, int q_mc) {
   extern __shared__ __align__(16) float smem[];
   pdl_launch_dependents();
   const ColTile t = pl.tiles3[blockIdx.x];
@@ -801,13 +801,17 @@ k_q_from_mt(DevPlan pl, PtrSlot ps, const float* __restrict__ p_mem, float* __re
         const float4 v = __ldcg(reinterpret_cast<const float4*>(src + (size_t)b * stride) + f);
         sum.x += v.x; sum.y += v.y; sum.z += v.z; sum.w += v.w;
       }
-      dst[4 * f] = sum.x; dst[4 * f + 1] = sum.y; dst[4 * f + 2] = sum.z; dst[4 * f + 3] = sum.w;
+      if (q_mc) {  // pushed into every rank's receive buffer (q_mem is a multicast address)
+        mm_st1(dst + 4 * f, sum.x); mm_st1(dst + 4 * f + 1, sum.y); mm_st1(dst + 4 * f + 2, sum.z); mm_st1(dst + 4 * f + 3, sum.w);
+      } else {
+        dst[4 * f] = sum.x; dst[4 * f + 1] = sum.y; dst[4 * f + 2] = sum.z; dst[4 * f + 3] = sum.w;
+      }
     }
   } else {
     for (int e = threadIdx.x; e < count; e += kThreads3) {
       float sum = 0.f;
       for (int b = 0; b < nb; ++b) sum += __ldcg(src + (size_t)b * stride + e);
-      dst[e] = sum;
+      st_out(dst + e, sum, q_mc != 0);
     }
   }
   if (threadIdx.x == 0) done[t.pad0] = 0;
@@ -1105,6 +1109,23 @@ k_peer_allreduce(PeerArgs a, float* __restrict__ out, long long n, int rank, int
   }
 }
 
+
+// "Push" of a locally produced buffer: this rank's slot of every rank's receive buffer (one multimem.st per element).
+// Used when the producing kernels could not push their results themselves (direct-load fallbacks, separate second
+// stage of K3): same values, one small extra launch.
+__global__ void __launch_bounds__(kThreads)
+k_push_to_all(const float* __restrict__ local, float* __restrict__ mc, long long n) {
+  const long long stride = (long long)gridDim.x * kThreads;
+  const long long n4 = n >> 2;
+  const bool vec = ((reinterpret_cast<uintptr_t>(local) | reinterpret_cast<uintptr_t>(mc)) & 15) == 0;
+  if (vec) {
+    for (long long i = (long long)blockIdx.x * kThreads + threadIdx.x; i < n4; i += stride)
+      mm_st4(mc + 4 * i, __ldcg(reinterpret_cast<const float4*>(local) + i));
+    for (long long i = (n4 << 2) + (long long)blockIdx.x * kThreads + threadIdx.x; i < n; i += stride) mm_st1(mc + i, __ldcg(local + i));
+  } else {
+    for (long long i = (long long)blockIdx.x * kThreads + threadIdx.x; i < n; i += stride) mm_st1(mc + i, __ldcg(local + i));
+  }
+}
 
 // Stand-alone form of the all-reduce-on-load (fallback for steps whose consumer kernel cannot take it in: direct-load
 // kernels on unaligned tensors, matrices too tall for the register-resident Gram-Schmidt): one flag barrier, then

@@ -47,6 +47,7 @@ struct StreamPlan {
   const int* direct_row_pre;  // n_direct + 1 prefix sums of their row counts
   int n_direct;
   int split_max_sub;     // K1: units with at most this many row groups are also cut by columns (0: never)
+  int out_mc;            // K1: p_mem and flat are multicast addresses (results are pushed to every rank, see st_out)
 };
 
 // The rows of all such matrices form one list of items; warp w of CTA b takes items (k * gridDim + b) * 8 + w, so a
@@ -97,7 +98,7 @@ __device__ __forceinline__ void direct_p_from_m(const DevPlan& pl, const PtrSlot
 #pragma unroll
     for (int c = 0; c < R; ++c) {
       const float t = warp_sum(acc[c]);
-      if (lane == 0 && c < r) p_mem[md.p_off + (size_t)row * r + c] = t;
+      if (lane == 0 && c < r) st_out(p_mem + md.p_off + (size_t)row * r + c, t, sp.out_mc != 0);
     }
   }
 }
@@ -146,7 +147,7 @@ __device__ __forceinline__ void stream_vec_side_job(const StreamPlan& sp, const 
     float* f = sp.flat + vt.flat_off;
     if (sp.vec_mode == 1) {
       const float* s = ps.vin[vt.tensor] + vt.start;
-      for (int i = threadIdx.x; i < vt.count; i += NT) f[i] = s[i];
+      for (int i = threadIdx.x; i < vt.count; i += NT) st_out(f + i, s[i], sp.out_mc != 0);
     } else if (sp.vec_mode == 2) {
       const float* g = ps.vg[vt.tensor] + vt.start;
       const float* e = ps.ve[vt.tensor] + vt.start;
@@ -154,7 +155,7 @@ __device__ __forceinline__ void stream_vec_side_job(const StreamPlan& sp, const 
       for (int i = threadIdx.x; i < vt.count; i += NT) {
         const float v = g[i] + e[i];
         send[i] = v;
-        f[i] = v;
+        st_out(f + i, v, sp.out_mc != 0);
       }
     } else if (sp.vec_mode == 3) {
       float* d = ps.vout[vt.tensor] + vt.start;
@@ -631,7 +632,7 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
           const int idx = lane / LPV;
           const int a = g + idx / R, c = idx % R;
           if (cs == 1) {
-            if (a < nr && c < r) P[(size_t)(u_a + rbase + a) * r + c] = tot;
+            if (a < nr && c < r) st_out(P + (size_t)(u_a + rbase + a) * r + c, tot, sp.out_mc != 0);
           } else {
             sm.part[(slot * kSplitItems + j) * 32 + g * R + idx] = tot;
           }
@@ -649,7 +650,7 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
           float t = pp[0];
           for (int sl = 1; sl < cs; ++sl) t += pp[sl * 32];
           const int a = lane / R, c = lane % R;
-          if (sub * ROWS + a < u_n && c < r) P[(size_t)(u_a + sub * ROWS + a) * r + c] = t;
+          if (sub * ROWS + a < u_n && c < r) st_out(P + (size_t)(u_a + sub * ROWS + a) * r + c, t, sp.out_mc != 0);
         }
       }
       pphase ^= 1u << slot;

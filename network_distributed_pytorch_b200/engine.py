@@ -107,6 +107,14 @@ class CudaPlan:
         _lib.check(self._lib.psgd_p_from_m_peer(self._h, peer.handle, p_mem.data_ptr(), q_mem.data_ptr(), int(fuse_add),
                                                 _stream(self.device)), self._lib)
 
+    def p_from_m_push(self, peer, q_mem, fuse_add=False, with_flat=True, reduce_q_first=False):
+        _lib.check(self._lib.psgd_p_from_m_push(self._h, peer.handle, q_mem.data_ptr(), int(fuse_add), int(with_flat),
+                                                int(reduce_q_first), _stream(self.device)), self._lib)
+
+    def q_from_mt_push(self, peer, p_mem):
+        _lib.check(self._lib.psgd_q_from_mt_push(self._h, peer.handle, p_mem.data_ptr(), self.workspace().data_ptr(),
+                                                 _stream(self.device)), self._lib)
+
     def orthogonalize_peer(self, peer, p_mem, flat_out):
         _lib.check(self._lib.psgd_orthogonalize_peer(self._h, peer.handle, p_mem.data_ptr(),
                                                      flat_out.data_ptr() if flat_out is not None else None,

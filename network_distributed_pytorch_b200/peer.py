@@ -5,19 +5,22 @@ buffer and signal pad).  Two families of implementation, all this package's own 
 
 * fused (default): no all-reduce launch at all.  The Gram-Schmidt kernel takes a flag barrier and loads its rows
   summed over the ranks; the streamed finalize kernel (and the P = M Q kernel of a later power iteration) does the same
-  for Q in its prologue (psgd_orthogonalize_peer / psgd_finalize_peer / psgd_p_from_m_peer).  The sum is formed either
-  by the NVSwitch (``multimem.ld_reduce``, mode "multimem") or by one load per rank added in rank order (mode "pull",
-  bit-identical on all ranks by construction, needs no multicast mapping).
+  for Q in its prologue (psgd_orthogonalize_peer / psgd_finalize_peer / psgd_p_from_m_peer).  Three ways of forming the
+  sum: "push" -- the producing kernels store their results with ``multimem.st`` into slot [rank] of every rank's receive
+  buffer while they run, and after the barrier the consumers add W local slots in slot order (nothing crosses NVLink
+  on the critical path; needs the multicast mapping); "multimem" -- one ``multimem.ld_reduce`` per element, the
+  NVSwitch adds the copies; "pull" -- one load per rank added in rank order (needs no multicast mapping).  Push and
+  pull are bit-identical on all ranks by construction, multimem was measured to be.
 * kernel: the round-1 stand-alone kernels between the phases (two-shot through the multicast mapping where the fabric
   has one, else one-shot pull) -- kept as a comparison point and as the parity cross-check.
 
 Set-up is a collective; if it fails on any rank every rank falls back to torch.distributed.all_reduce (NCCL).
 
 PSGD_PEER_ALLREDUCE: 0 = NCCL, 1 = this module, unset = this module from 2 ranks on (inside one node).
-PSGD_PEER_MODE: pull | multimem | kernel; unset: multimem where the fabric gives the buffers a multicast mapping, else
-pull.  Measured DistilBERT r=4 step on B200s (profiles/r02_allreduce_modes.md): one GPU 0.237 ms; two GPUs fused-multimem
-0.270, fused-pull 0.272, NCCL 0.274, stand-alone kernels 0.290; eight GPUs fused-multimem 0.291, stand-alone kernels
-0.294, NCCL 0.308, fused-pull 0.328 (reads (W-1) x the message).  multimem sums came out bit-identical on all eight ranks.
+PSGD_PEER_MODE: push | multimem | pull | kernel; unset: push where the fabric gives the buffers a multicast mapping,
+else pull.  Measured DistilBERT r=4 step on B200s (profiles/r02_allreduce_modes.md): one GPU 0.237 ms; two GPUs push 0.267,
+multimem 0.270, pull 0.272, NCCL 0.274, stand-alone kernels 0.290; eight GPUs push 0.280, multimem 0.291, stand-alone
+kernels 0.294, NCCL 0.308, pull 0.328 (reads (W-1) x the message).  multimem sums came out bit-identical on all eight ranks.
 """
 import ctypes
 import os
@@ -29,7 +32,7 @@ from . import _lib
 
 _SLOT0 = 256          # first signal-pad slot used by this package (torch's own barrier uses the low slots)
 MAX_WORLD = 8
-_MODE_IDS = {"multimem": 1, "pull": 2}
+_MODE_IDS = {"multimem": 1, "pull": 2, "push": 3}
 
 
 class PeerExchange:
@@ -42,8 +45,10 @@ class PeerExchange:
         self._lib = _lib.load()
         group = dist.group.WORLD
         pad4 = lambda n: (max(n, 4) + 3) // 4 * 4
-        self.buf = [symm.empty(pad4(n_pf), dtype=torch.float32, device=device),
-                    symm.empty(pad4(n_q), dtype=torch.float32, device=device)]
+        self.stride = [pad4(n_pf), pad4(n_q)]
+        slots = self.world if mode in ("push", "auto") else 1  # push: one receive slot per source rank
+        self.buf = [symm.empty(slots * self.stride[0], dtype=torch.float32, device=device),
+                    symm.empty(slots * self.stride[1], dtype=torch.float32, device=device)]
         self.hdl = [symm.rendezvous(b, group) for b in self.buf]
         for h in self.hdl:
             if len(h.buffer_ptrs) != self.world or h.signal_pad_size < 4 * (_SLOT0 + 2 * MAX_WORLD):
@@ -54,8 +59,8 @@ class PeerExchange:
         self._mc = [int(getattr(h, "multicast_ptr", 0) or 0) for h in self.hdl]
         have_mc = all(self._mc) and os.environ.get("PSGD_PEER_MULTICAST", "1") == "1"
         if mode == "auto":
-            mode = "multimem" if have_mc else "pull"
-        if mode == "multimem" and not have_mc:
+            mode = "push" if have_mc else "pull"
+        if mode in ("multimem", "push") and not have_mc:
             mode = "pull"
         self.fused = mode in _MODE_IDS
         if self.fused:
@@ -77,7 +82,15 @@ class PeerExchange:
             pad = h.get_signal_pad(self.rank, (h.signal_pad_size // 4,), torch.int32)
             pad[_SLOT0 : _SLOT0 + 2 * MAX_WORLD].zero_()
         self._h = None
-        if self.fused:
+        self.push = mode == "push"
+        if self.push:
+            handle = ctypes.c_void_p()
+            _lib.check(self._lib.psgd_peer_create_push(
+                self.world, self.rank, device.index, ctypes.c_void_p(self.buf[0].data_ptr()), ctypes.c_void_p(self._mc[0]),
+                self.stride[0], self._sig[0], ctypes.c_void_p(self.buf[1].data_ptr()), ctypes.c_void_p(self._mc[1]),
+                self.stride[1], self._sig[1], _SLOT0, ctypes.byref(handle)), self._lib)
+            self._h = handle
+        elif self.fused:
             handle = ctypes.c_void_p()
             _lib.check(self._lib.psgd_peer_create(
                 self.world, self.rank, device.index, self._in[0], self._sig[0],
@@ -97,7 +110,8 @@ class PeerExchange:
                 pass
 
     def describe(self):
-        return {"fused-pull": "none as a launch: summed on load inside the Gram-Schmidt and finalize kernels (one load per rank, rank order)",
+        return {"fused-push": "none as a launch: pushed by the producing kernels (multimem.st), summed from local slots inside the Gram-Schmidt and finalize kernels",
+                "fused-pull": "none as a launch: summed on load inside the Gram-Schmidt and finalize kernels (one load per rank, rank order)",
                 "fused-multimem": "none as a launch: summed on load inside the Gram-Schmidt and finalize kernels (multimem.ld_reduce in the NVSwitch)",
                 "kernel-multicast": "own kernel, NVSwitch multicast (multimem), two-shot",
                 "kernel-pull": "own kernel, peer pull"}[self.kind]
@@ -143,8 +157,8 @@ def try_setup(device, n_pf, n_q):
     if device.type != "cuda" or dist.get_backend() != "nccl":
         return None
     mode = os.environ.get("PSGD_PEER_MODE", "auto")
-    if mode not in ("auto", "pull", "multimem", "kernel"):
-        raise ValueError("PSGD_PEER_MODE must be auto, pull, multimem or kernel")
+    if mode not in ("auto", "push", "pull", "multimem", "kernel"):
+        raise ValueError("PSGD_PEER_MODE must be auto, push, pull, multimem or kernel")
     ex, ok = None, 1
     try:
         ex = PeerExchange(device, n_pf, n_q, mode)

@@ -201,6 +201,7 @@ class PowerSGDReducer(Reducer):
             self._call_cache = (sig, plan)
         flat = self._flat
         px = self._peer
+        push = px is not None and px.push
         if px is not None:  # phase inputs live in symmetric memory, results land in p_memory || flat and q_memory
             n_pf = self._p_and_flat.nelement()
             p_in, flat_in, q_in = px.buf[0][: plan.p_elems], px.buf[0][plan.p_elems : n_pf], px.buf[1][: plan.q_elems]
@@ -210,7 +211,7 @@ class PowerSGDReducer(Reducer):
         # [For Rank 1] the flat buffer is gathered inside the first P = M Q launch and travels with P in one collective
         # (upstream packs after step 4 and runs its own async all-reduce, reducer.py:131-133; the sums are the same)
         fold = hasattr(plan, "p_from_m_pack")
-        if not fold:
+        if not fold and not push:
             if fused:
                 plan.pack_vec_fused(flat_in)
             else:
@@ -232,7 +233,10 @@ class PowerSGDReducer(Reducer):
             elif fused_px:
                 # Step 3; from the second power iteration on the kernel first sums Q over the ranks (step 7 of the
                 # previous iteration) in its prologue
-                if it == 0:
+                if push:  # results go straight into every rank's receive buffer
+                    plan.p_from_m_push(px, self.q_memory, fuse_add=(fused and it == 0), with_flat=(it == 0),
+                                       reduce_q_first=(it > 0))
+                elif it == 0:
                     plan.p_from_m_pack(p_in, self.q_memory, flat_in, fuse_add=fused)
                 else:
                     plan.p_from_m_peer(px, p_in, self.q_memory)
@@ -259,7 +263,10 @@ class PowerSGDReducer(Reducer):
                 # Step 5 (reducer.py:136-137) P_hat <- ORTHOGONALIZE(P / n_workers)
                 plan.orthogonalize(self.p_memory, world)
             # Step 6 (reducer.py:140-142) Q <- M^T P_hat
-            plan.q_from_mt(self.p_memory, q_in)
+            if push:
+                plan.q_from_mt_push(px, self.p_memory)
+            else:
+                plan.q_from_mt(self.p_memory, q_in)
             # Step 7 (reducer.py:145-147) ALL_REDUCE_MEAN(Q); the divide is applied while Q is staged
             if fused_px:
                 pass  # summed on load by the next streamed kernel (finalize, or the next iteration's P = M Q)

@@ -11,6 +11,7 @@ if [ -n "$EXTRA" ]; then
   run fused_pull_light PSGD_PEER_ALLREDUCE=1 PSGD_PEER_MODE=pull PSGD_PEER_LIGHT=1
   run fused_multimem_light PSGD_PEER_ALLREDUCE=1 PSGD_PEER_MODE=multimem PSGD_PEER_LIGHT=1
 fi
+run fused_push PSGD_PEER_ALLREDUCE=1 PSGD_PEER_MODE=push
 run fused_pull PSGD_PEER_ALLREDUCE=1 PSGD_PEER_MODE=pull
 run fused_multimem PSGD_PEER_ALLREDUCE=1 PSGD_PEER_MODE=multimem
 if [ -z "$QUICK" ]; then

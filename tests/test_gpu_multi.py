@@ -114,6 +114,7 @@ print("rank", rank, "ok", "peer=%s" % (red._peer is not None), "kind=%s" % (red.
 
 
 MODES = {  # name -> environment
+    "fused-push": {"PSGD_PEER_ALLREDUCE": "1", "PSGD_PEER_MODE": "push"},
     "fused-pull": {"PSGD_PEER_ALLREDUCE": "1", "PSGD_PEER_MODE": "pull"},
     "fused-multimem": {"PSGD_PEER_ALLREDUCE": "1", "PSGD_PEER_MODE": "multimem"},
     "kernel-multicast": {"PSGD_PEER_ALLREDUCE": "1", "PSGD_PEER_MODE": "kernel"},
