@@ -88,6 +88,7 @@ struct psgd_plan {
   bool stream_ok = false;              // static: smem configuration valid and something qualifies
   bool stream1_now = false, stream4_now = false, stream1f_now = false;  // per step: every qualifying matrix is 16-byte aligned
   std::vector<char> eligible;
+  bool has_chunked = false;  // some matrix streams in two column halves (its Q does not fit the stage in one piece)
   std::vector<StreamTask> tasks1, tasks4;
   std::vector<int4> tiles1_fb, tiles4_fb;  // direct-load tiles of the matrices that do not qualify
   std::vector<int> direct_ids;             // ... except the tiny ones, done as a side job of the streamed launch
@@ -241,9 +242,13 @@ void build_stream_tasks(const psgd_plan* p, int rows_per_sub, int slot_bytes, st
     const long long div = last ? div0 * tail_div : div0;
     const MatDesc& md = p->mats[i];
     const long long row_bytes = (long long)md.m * 4;
-    const int rpu = (int)std::max<long long>(1, slot_bytes / row_bytes);
+    const int nchunk = md.pad_ > 1 ? md.pad_ : 1;
+    // rows per ring unit of one pass; a column-chunked matrix streams every task once per column half and stages a
+    // (large) Q half each time, so its tasks are kept longer
+    const int rpu = (int)std::max<long long>(1, slot_bytes / (row_bytes / nchunk));
     const int sub_per_unit = (rpu + rows_per_sub - 1) / rows_per_sub;
-    const long long min_units = last ? std::min(min_units0, (tail_min_bytes + rpu * row_bytes - 1) / (rpu * row_bytes)) : min_units0;
+    long long min_units = last ? std::min(min_units0, (tail_min_bytes + rpu * row_bytes - 1) / (rpu * row_bytes)) : min_units0;
+    if (nchunk > 1) min_units = std::max<long long>(min_units, env_ll("PSGD_CHUNK_MIN_UNITS", 4));
     int row = 0;
     while (row < md.n) {
       const long long want = std::max<long long>(1, remaining / std::max<long long>(1, div));
@@ -541,12 +546,26 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
     p->eligible.assign(n_mat, 0);
     long long qb = 0;
     if (env_ll("PSGD_STREAM", 1) != 0) {
+      const bool chunk_ok = env_ll("PSGD_STREAM_CHUNK", 1) != 0;
       for (int i = 0; i < n_mat; ++i) {
-        const MatDesc& md = p->mats[i];
+        MatDesc& md = p->mats[i];
+        md.pad_ = 1;
+        if (!(md.n > 0 && md.m > 0 && md.m % 4 == 0)) continue;
         const long long qs = (long long)R * q_pitch(md.m, R) * 4;
-        if (md.n > 0 && md.m > 0 && md.m % 4 == 0 && (long long)md.m * 4 <= std::min(slot, slot1) && qs <= q_cap) {
+        if ((long long)md.m * 4 <= std::min(slot, slot1) && qs <= q_cap) {
           p->eligible[i] = 1;
           qb = std::max(qb, qs);
+          continue;
+        }
+        // Q too large for the stage in one piece (wide matrix, high rank): stream the matrix in two column halves,
+        // one Q half staged at a time (psgd_stream.cuh, column-chunked tasks)
+        const int w = md.m / 2;
+        const long long qs2 = (long long)R * q_pitch(w, R) * 4;
+        if (chunk_ok && md.m % 8 == 0 && i < kMatCache && (long long)w * 4 <= std::min(slot, slot1) && qs2 <= q_cap) {
+          p->eligible[i] = 1;
+          md.pad_ = 2;
+          p->has_chunked = true;
+          qb = std::max(qb, qs2);
         }
       }
     }
@@ -588,8 +607,8 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
   }
 
   {  // K2 routing: register-resident single CTA, register-resident cluster, or generic cluster
-    const int rpt = R <= 8 ? 4 : 2;
-    p->orth_tall_cluster = (R == 16) ? kOrthClusterMax : kOrthCluster;  // R = 16 keeps only 2 rows per thread
+    const int rpt = 4;  // rows per thread of the register-resident Gram-Schmidt kernels (1024 threads, 512 at R = 16)
+    p->orth_tall_cluster = (R == 16) ? kOrthClusterMax : kOrthCluster;  // R = 16: 512 threads x 4 rows per CTA
     p->orth_merge = env_ll("PSGD_ORTH_MERGE", 1) != 0;
     p->pdl = env_ll("PSGD_PDL", 1) != 0;
     // measured: pays at R >= 8 (twice the FMAs per byte: DistilBERT r=8 step 291 -> 284 us), costs 1-3 % at R <= 4
@@ -599,8 +618,8 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
     for (int i = 0; i < n_mat; ++i) {
       const long long nn = p->mats[i].n;
       if (nn == 0 || p->mats[i].m == 0) continue;
-      if (R <= 16 && nn <= (long long)kOrthSmallThreads * rpt) p->orth_small.push_back(i);
-      else if (R <= 16 && nn <= (long long)p->orth_tall_cluster * kOrthSmallThreads * rpt) p->orth_tall.push_back(i);
+      if (R <= 16 && nn <= (long long)orth_threads(R) * rpt) p->orth_small.push_back(i);
+      else if (R <= 16 && nn <= (long long)p->orth_tall_cluster * orth_threads(R) * rpt) p->orth_tall.push_back(i);
       else p->orth_generic.push_back(i);
     }
   }
@@ -1075,9 +1094,9 @@ static int orth_impl(psgd_plan* p, float* p_mem, float n_workers, psgd_stream st
   if (n_small && !merged) {
     const unsigned grid = (unsigned)n_small;
     if (p->R <= 8) {
-      DISPATCH_R8(p->R, { CU(launch_ex(k_orth_small<RR, 4>, dim3(grid), dim3(kOrthSmallThreads), 0, s, 1, p->pdl, dp, (const int*)p->d_orth_small, p_mem, n_workers)); });
+      DISPATCH_R8(p->R, { CU(launch_ex(k_orth_small<RR, 4>, dim3(grid), dim3(orth_threads(p->R)), 0, s, 1, p->pdl, dp, (const int*)p->d_orth_small, p_mem, n_workers)); });
     } else {
-      CU(launch_ex(k_orth_small<16, 2>, dim3(grid), dim3(kOrthSmallThreads), 0, s, 1, p->pdl, dp, (const int*)p->d_orth_small, p_mem, n_workers));
+      CU(launch_ex(k_orth_small<16, 4>, dim3(grid), dim3(orth_threads(p->R)), 0, s, 1, p->pdl, dp, (const int*)p->d_orth_small, p_mem, n_workers));
     }
     if (check_launch("k_orth_small")) return 1;
   }
@@ -1092,11 +1111,11 @@ static int orth_impl(psgd_plan* p, float* p_mem, float n_workers, psgd_stream st
     if (pass == 0) {
       const int* d_small = p->d_orth_small;
       if (p->R <= 8) {
-        DISPATCH_R8(p->R, { CU(launch_ex(k_orth_tall<RR, 4>, grid, dim3(kOrthSmallThreads), 0, s, csz, p->pdl, dp, d_ids, n_tall, d_small, n_ride, p_mem, n_workers)); });
+        DISPATCH_R8(p->R, { CU(launch_ex(k_orth_tall<RR, 4>, grid, dim3(orth_threads(p->R)), 0, s, csz, p->pdl, dp, d_ids, n_tall, d_small, n_ride, p_mem, n_workers)); });
       } else {
-        if (!p->orth16_attr) CU(cudaFuncSetAttribute((const void*)k_orth_tall<16, 2>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        if (!p->orth16_attr) CU(cudaFuncSetAttribute((const void*)k_orth_tall<16, 4>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
         p->orth16_attr = true;
-        CU(launch_ex(k_orth_tall<16, 2>, grid, dim3(kOrthSmallThreads), 0, s, csz, p->pdl, dp, d_ids, n_tall, d_small, n_ride, p_mem, n_workers));
+        CU(launch_ex(k_orth_tall<16, 4>, grid, dim3(orth_threads(p->R)), 0, s, csz, p->pdl, dp, d_ids, n_tall, d_small, n_ride, p_mem, n_workers));
       }
     } else {
       // the generic kernel has no dependency wait of its own: plain stream order
@@ -1383,7 +1402,8 @@ int psgd_p_from_m_push(psgd_plan* p, psgd_peer* peer, float* q_mem, int fuse_add
   const bool tc1 = p->tc && (p->tc_mask & 1) && (fuse_add ? p->tcf_now : p->tc_now);
   // The streamed kernel can store straight through the multicast address when it is the only producer; otherwise
   // the results are written to this rank's own slot and pushed by one small extra launch.
-  const bool direct = !tc1 && (fuse_add ? p->stream1f_now : p->stream1_now) && p->tiles1_fb.empty() && !p->tiles1.empty();
+  const bool direct = !tc1 && (fuse_add ? p->stream1f_now : p->stream1_now) && p->tiles1_fb.empty() && !p->tiles1.empty() &&
+                      !p->has_chunked;  // (a column-chunked matrix adds to its own P in the second pass: ordinary memory only)
   psgd_peer* pq = reduce_q_first ? peer : nullptr;
   if (direct) return p_from_m_impl(p, mcp, q_mem, fuse_add, 1.0f, want_flat ? mcp + p->p_total : nullptr, stream, pq, true);
   if (p_from_m_impl(p, loc, q_mem, fuse_add, 1.0f, want_flat ? loc + p->p_total : nullptr, stream, pq, false)) return 1;
@@ -1464,7 +1484,7 @@ int psgd_orthogonalize_peer(psgd_plan* p, psgd_peer* peer, float* p_mem, float* 
   pf.sym_off = p->p_total;
   pf.n = want_flat ? p->v_total : 0;
   pf.div = world;
-  const int n_flat_ctas = want_flat ? (int)((p->v_total + kPeerFlatPerCta - 1) / kPeerFlatPerCta) : 0;
+  const int n_flat_ctas = want_flat ? (int)((p->v_total + peer_flat_per_cta(p->R) - 1) / peer_flat_per_cta(p->R)) : 0;
   const int tcs = p->orth_tall_cluster;
   const bool merged = n_tall > 0 && (n_tall + (n_small + n_flat_ctas + tcs - 1) / tcs) * tcs <= std::max(p->orth_merge_max_ctas, 148);
   if (n_tall == 0 || !merged) {  // small matrices (and, without tall ones, the flat buffer) in a plain launch
@@ -1473,9 +1493,9 @@ int psgd_orthogonalize_peer(psgd_plan* p, psgd_peer* peer, float* p_mem, float* 
     const unsigned grid = (unsigned)(n_small + (flat_here ? n_flat_ctas : 0));
     if (grid) {
       if (p->R <= 8) {
-        DISPATCH_R8(p->R, { CU(launch_ex(k_orth_small_peer<RR, 4>, dim3(grid), dim3(kOrthSmallThreads), 0, s, 1, p->pdl, dp, (const int*)p->d_orth_small, n_small, p_mem, world, pm, pf_small)); });
+        DISPATCH_R8(p->R, { CU(launch_ex(k_orth_small_peer<RR, 4>, dim3(grid), dim3(orth_threads(p->R)), 0, s, 1, p->pdl, dp, (const int*)p->d_orth_small, n_small, p_mem, world, pm, pf_small)); });
       } else {
-        CU(launch_ex(k_orth_small_peer<16, 2>, dim3(grid), dim3(kOrthSmallThreads), 0, s, 1, p->pdl, dp, (const int*)p->d_orth_small, n_small, p_mem, world, pm, pf_small));
+        CU(launch_ex(k_orth_small_peer<16, 4>, dim3(grid), dim3(orth_threads(p->R)), 0, s, 1, p->pdl, dp, (const int*)p->d_orth_small, n_small, p_mem, world, pm, pf_small));
       }
       if (check_launch("k_orth_small_peer")) return 1;
     }
@@ -1484,10 +1504,10 @@ int psgd_orthogonalize_peer(psgd_plan* p, psgd_peer* peer, float* p_mem, float* 
     const int n_ride = merged ? n_small : 0;
     const dim3 grid((unsigned)(n_tall + (n_ride + n_flat_ctas + tcs - 1) / tcs) * tcs);
     if (p->R <= 8) {
-      DISPATCH_R8(p->R, { CU(launch_ex(k_orth_tall_peer<RR, 4>, grid, dim3(kOrthSmallThreads), 0, s, tcs, p->pdl, dp, (const int*)p->d_orth_tall, n_tall, (const int*)p->d_orth_small, n_ride, p_mem, world, pm, pf)); });
+      DISPATCH_R8(p->R, { CU(launch_ex(k_orth_tall_peer<RR, 4>, grid, dim3(orth_threads(p->R)), 0, s, tcs, p->pdl, dp, (const int*)p->d_orth_tall, n_tall, (const int*)p->d_orth_small, n_ride, p_mem, world, pm, pf)); });
     } else {
-      CU(cudaFuncSetAttribute((const void*)k_orth_tall_peer<16, 2>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
-      CU(launch_ex(k_orth_tall_peer<16, 2>, grid, dim3(kOrthSmallThreads), 0, s, tcs, p->pdl, dp, (const int*)p->d_orth_tall, n_tall, (const int*)p->d_orth_small, n_ride, p_mem, world, pm, pf));
+      CU(cudaFuncSetAttribute((const void*)k_orth_tall_peer<16, 4>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+      CU(launch_ex(k_orth_tall_peer<16, 4>, grid, dim3(orth_threads(p->R)), 0, s, tcs, p->pdl, dp, (const int*)p->d_orth_tall, n_tall, (const int*)p->d_orth_small, n_ride, p_mem, world, pm, pf));
     }
     if (check_launch("k_orth_tall_peer")) return 1;
   }

@@ -10,7 +10,10 @@ constexpr int kThreads = 256;      // CTA size of the streaming kernels (8 warps
 constexpr int kWarps = kThreads / 32;
 constexpr int kConsumerWarps = 8;   // consumer warps of the streamed kernels (psgd_stream.cuh); warp 8 is the producer
 constexpr int kOrthThreads = 512;  // CTA size of the generic (global-memory) Gram-Schmidt kernel
-constexpr int kOrthSmallThreads = 1024;  // CTA size of the register-resident Gram-Schmidt kernels
+constexpr int kOrthSmallThreads = 1024;  // CTA size of the register-resident Gram-Schmidt kernels (R <= 8)
+// At R = 16 the same kernels run 512 threads x 4 rows (same rows per CTA): 128 registers per thread leave room for the
+// rolled step loop with rotating columns; the unrolled 1024 x 2 form spent its time fetching instructions (K2 118 us).
+__host__ __device__ constexpr int orth_threads(int R) { return R >= 16 ? 512 : kOrthSmallThreads; }
 constexpr int kOrthCluster = 8;    // CTAs per matrix (one thread-block cluster)
 constexpr int kOrthClusterMax = 16;  // non-portable cluster size used for tall matrices at R = 16
 

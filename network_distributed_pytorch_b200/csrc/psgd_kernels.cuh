@@ -328,7 +328,7 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
   // 160 KB of SASS).  To keep the rows in registers under a runtime step index the columns rotate instead: the column
   // being normalised is always register 0, the unfinished ones follow, finished ones queue up at the back, and after R
   // rotations everything is back in place.
-  if constexpr (R <= 8) {
+  if constexpr (R <= 16) {
 #pragma unroll 1
   for (int i = 0; i < R; ++i) {
     if (i < r) {  // uniform over the CTA / cluster
@@ -401,7 +401,7 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
     }
   }
   } else {
-  // R = 16 (2 rows per thread) has no registers to spare for the rotation: unrolled steps
+  // larger R: unrolled steps
 #pragma unroll
   for (int i = 0; i < R; ++i) {
     if (i < r) {  // uniform over the CTA / cluster
@@ -486,7 +486,7 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
 
 // one CTA per "small" matrix (n <= blockDim * RPT)
 template <int R, int RPT>
-__global__ void __launch_bounds__(kOrthSmallThreads)
+__global__ void __launch_bounds__(orth_threads(R))
 k_orth_small(DevPlan pl, const int* __restrict__ ids, float* __restrict__ p_mem, float world) {
   __shared__ __align__(16) float wsum[32 * R];
   __shared__ __align__(16) float part[2 * kOrthClusterMax * R];
@@ -505,10 +505,10 @@ struct PeerFlat {
   long long n;         // elements
   float div;           // n_workers
 };
-constexpr int kPeerFlatPerCta = kOrthSmallThreads * 4;
+__host__ __device__ constexpr int peer_flat_per_cta(int R) { return orth_threads(R) * 4; }
 
 __device__ __forceinline__ void peer_flat_job(const PeerLoad& pm, const PeerFlat& pf, int idx) {
-  const long long e = (long long)idx * kPeerFlatPerCta + (long long)threadIdx.x * 4;
+  const long long e = ((long long)idx * blockDim.x + threadIdx.x) * 4;
   if (e >= pf.n) return;
   if (e + 4 <= pf.n && ((pf.sym_off & 3) == 0) && ((reinterpret_cast<uintptr_t>(pf.out) & 15) == 0)) {
     float4 v = peer_sum4(pm, pf.sym_off + e);
@@ -523,7 +523,7 @@ __device__ __forceinline__ void peer_flat_job(const PeerLoad& pm, const PeerFlat
 // grid tells every peer "my P is written" and waits for theirs (one flag barrier, no extra launch, no copy), then
 // every CTA reads its rows summed over the ranks.  One CTA per small matrix.
 template <int R, int RPT>
-__global__ void __launch_bounds__(kOrthSmallThreads)
+__global__ void __launch_bounds__(orth_threads(R))
 k_orth_small_peer(DevPlan pl, const int* __restrict__ ids, int n_small, float* __restrict__ p_mem, float world,
                   PeerLoad pm, PeerFlat pf) {
   __shared__ __align__(16) float wsum[32 * R];
@@ -544,7 +544,7 @@ k_orth_small_peer(DevPlan pl, const int* __restrict__ ids, int n_small, float* _
 // fits one wave, they ride on the same launch: the clusters behind the n_tall cooperative ones are mere containers whose
 // CTAs each take one small matrix and never touch the cluster barrier.
 template <int R, int RPT>
-__global__ void __launch_bounds__(kOrthSmallThreads)
+__global__ void __launch_bounds__(orth_threads(R))
 k_orth_tall(DevPlan pl, const int* __restrict__ ids, int n_tall, const int* __restrict__ small_ids, int n_small,
             float* __restrict__ p_mem, float world) {
   __shared__ __align__(16) float wsum[32 * R];
@@ -573,7 +573,7 @@ k_orth_tall(DevPlan pl, const int* __restrict__ ids, int n_tall, const int* __re
 
 // tall matrices one cluster each, small ones in container clusters, then the flat buffer (see k_orth_small_peer)
 template <int R, int RPT>
-__global__ void __launch_bounds__(kOrthSmallThreads)
+__global__ void __launch_bounds__(orth_threads(R))
 k_orth_tall_peer(DevPlan pl, const int* __restrict__ ids, int n_tall, const int* __restrict__ small_ids, int n_small,
                  float* __restrict__ p_mem, float world, PeerLoad pm, PeerFlat pf) {
   __shared__ __align__(16) float wsum[32 * R];

@@ -172,6 +172,7 @@ constexpr int kDbgWords = 8;  // per CTA: t0, t1 (ns), cycles: desc wait, data w
 // what travels with a slot: an M unit {mat, row0, nrows > 0, rot}, a Q unit {mat, j0, -count, flags},
 // or the end marker {mat < 0}
 constexpr int kQFlagBulk = 1 << 16;  // Q unit: data was bulk-copied into the slot (else: fetch from global)
+constexpr int kQFlagChunk1 = 1 << 17;  // Q unit: second column half of a column-chunked matrix
 
 __device__ __forceinline__ unsigned long long gtime_ns() {
   unsigned long long t;
@@ -265,7 +266,7 @@ struct StreamSmem {
   uint64_t* desc;   // the slot's descriptor is published (well before its data lands)
   uint64_t* pbar;   // K1, column-split units: every consumer warp has delivered its partial sums of the slot's unit
   volatile int4* slot_desc;
-  struct MatInfo { const float* base; const float* q; const float* g; const float* e; int m; int r; long long pad; };
+  struct MatInfo { const float* base; const float* q; const float* g; const float* e; int m; int r; int nchunk; int pad; };
   MatInfo* matinfo;
   float* part;      // K1, column-split units: [slot][item][32] partial sums
 };
@@ -299,6 +300,7 @@ __device__ __forceinline__ StreamSmem::MatInfo mat_info(const DevPlan& pl, const
   mi.e = ps.e[mat];
   mi.m = md.m;
   mi.r = md.r;
+  mi.nchunk = md.pad_ > 1 ? md.pad_ : 1;
   mi.pad = 0;
   return mi;
 }
@@ -377,6 +379,7 @@ __device__ __forceinline__ void stream_setup(const DevPlan& pl, const PtrSlot& p
     sm.matinfo[i].e = ps.e[i];
     sm.matinfo[i].m = md.m;
     sm.matinfo[i].r = md.r;
+    sm.matinfo[i].nchunk = md.pad_ > 1 ? md.pad_ : 1;
   }
   __syncthreads();
 }
@@ -396,53 +399,77 @@ __device__ __forceinline__ void stream_producer(const DevPlan& pl, const PtrSlot
   int t = atomicAdd(&sp.counters[0], 1);
   StreamTask task = sp.tasks[t < sp.n_tasks ? t : 0];
   pdl_wait();  // nothing above depends on an earlier kernel of the stream; the copies below do
+  int prev_chunk = 0;
   while (t < sp.n_tasks) {
     const int t_next = atomicAdd(&sp.counters[0], 1);  // in flight while this task streams
     const StreamSmem::MatInfo mi = mat_info(pl, ps, sm, q_mem, task.mat);
-    const int m = mi.m;
-    if (task.mat != prev_mat) {  // new matrix: its Q goes first
-      const bool bulk = (reinterpret_cast<uintptr_t>(mi.q) & 15) == 0;
-      const int qrows = max(4, (sp.slot_bytes / (mi.r * 4)) & ~3);
-      for (int j0 = 0; j0 < m; j0 += qrows, ++it) {
-        const int cnt = min(qrows, m - j0);
+    const int ld = mi.m;                 // row length in global memory
+    const int nchunk = mi.nchunk;        // 1, or 2: the Q stage holds half of the columns at a time (wide matrix, high rank)
+    const int m = ld / nchunk;           // columns per pass = row length inside a slot
+    // Column-chunked matrix: the task's rows are streamed once per column half -- [Q_a][rows, left half][Q_b][rows,
+    // right half] -- each row segment with its own bulk copy.  Both passes cut the rows into the same units with the
+    // same warp rotation, so in K1 the lane that stored a row's partial sum in pass a adds pass b to its own store.
+    for (int chunk = 0; chunk < nchunk; ++chunk) {
+      const int col0 = chunk * m;
+      if (task.mat != prev_mat || chunk != prev_chunk) {  // new matrix (or column half): its Q goes first
+        const float* qsrc = mi.q + (size_t)col0 * mi.r;
+        const bool bulk = (reinterpret_cast<uintptr_t>(qsrc) & 15) == 0;
+        const int qrows = max(4, (sp.slot_bytes / (mi.r * 4)) & ~3);
+        for (int j0 = 0; j0 < m; j0 += qrows, ++it) {
+          const int cnt = min(qrows, m - j0);
+          const int slot = it % sp.n_slots;
+          const uint32_t phase = (uint32_t)(it / sp.n_slots) & 1u;
+          mbar_wait(&sm.empty[slot], phase ^ 1u);
+          sm.slot_desc[slot].x = task.mat; sm.slot_desc[slot].y = j0;
+          sm.slot_desc[slot].z = -cnt; sm.slot_desc[slot].w = (bulk ? kQFlagBulk : 0) | (chunk ? kQFlagChunk1 : 0);
+          mbar_arrive(&sm.desc[slot]);
+          if (bulk) {
+            const uint32_t bytes = (uint32_t)cnt * (uint32_t)mi.r * 4u;
+            mbar_arrive_expect_tx(&sm.full[slot], bytes);
+            bulk_g2s(sm.ring + (size_t)slot * sp.slot_bytes, qsrc + (size_t)j0 * mi.r, bytes, &sm.full[slot]);
+          } else {
+            mbar_arrive(&sm.full[slot]);  // every use of a slot completes one phase of each of its barriers
+          }
+        }
+        prev_mat = task.mat;
+        prev_chunk = chunk;
+      }
+      // FUSE: a unit carries the rows of grad and, right behind them, the same rows of err
+      const int rpu = max(1, sp.slot_bytes / (m * 4 * (FUSE ? 2 : 1)));
+      const int sub_per_unit = (rpu + ROWS - 1) / ROWS;
+      int rot = task.rot0;
+      for (int row0 = task.row_begin; row0 < task.row_end; row0 += rpu, ++it) {
+        const int nrows = min(rpu, task.row_end - row0);
         const int slot = it % sp.n_slots;
         const uint32_t phase = (uint32_t)(it / sp.n_slots) & 1u;
-        mbar_wait(&sm.empty[slot], phase ^ 1u);
-        sm.slot_desc[slot].x = task.mat; sm.slot_desc[slot].y = j0;
-        sm.slot_desc[slot].z = -cnt; sm.slot_desc[slot].w = bulk ? kQFlagBulk : 0;
+        mbar_wait(&sm.empty[slot], phase ^ 1u);  // passes at once on the first lap
+        const uint32_t bytes = (uint32_t)nrows * (uint32_t)m * 4u;
+        sm.slot_desc[slot].x = task.mat; sm.slot_desc[slot].y = row0;
+        sm.slot_desc[slot].z = nrows; sm.slot_desc[slot].w = rot | (chunk << 8);
         mbar_arrive(&sm.desc[slot]);
-        if (bulk) {
-          const uint32_t bytes = (uint32_t)cnt * (uint32_t)mi.r * 4u;
-          mbar_arrive_expect_tx(&sm.full[slot], bytes);
-          bulk_g2s(sm.ring + (size_t)slot * sp.slot_bytes, mi.q + (size_t)j0 * mi.r, bytes, &sm.full[slot]);
+        unsigned char* dst = sm.ring + (size_t)slot * sp.slot_bytes;
+        mbar_arrive_expect_tx(&sm.full[slot], FUSE ? 2u * bytes : bytes);
+        if (nchunk == 1) {
+          if (FUSE) {
+            bulk_g2s(dst, mi.g + (size_t)row0 * m, bytes, &sm.full[slot]);
+            bulk_g2s(dst + bytes, mi.e + (size_t)row0 * m, bytes, &sm.full[slot]);
+          } else {
+            bulk_g2s(dst, mi.base + (size_t)row0 * m, bytes, &sm.full[slot]);
+          }
         } else {
-          mbar_arrive(&sm.full[slot]);  // every use of a slot completes one phase of each of its barriers
+          const uint32_t rb = (uint32_t)m * 4u;  // one bulk copy per row segment
+          for (int i = 0; i < nrows; ++i) {
+            const size_t goff = (size_t)(row0 + i) * ld + col0;
+            if (FUSE) {
+              bulk_g2s(dst + (size_t)i * rb, mi.g + goff, rb, &sm.full[slot]);
+              bulk_g2s(dst + bytes + (size_t)i * rb, mi.e + goff, rb, &sm.full[slot]);
+            } else {
+              bulk_g2s(dst + (size_t)i * rb, mi.base + goff, rb, &sm.full[slot]);
+            }
+          }
         }
+        rot = (rot + sub_per_unit) % kConsumerWarps;
       }
-      prev_mat = task.mat;
-    }
-    // FUSE: a unit carries the rows of grad and, right behind them, the same rows of err
-    const int rpu = max(1, sp.slot_bytes / (m * 4 * (FUSE ? 2 : 1)));
-    const int sub_per_unit = (rpu + ROWS - 1) / ROWS;
-    int rot = task.rot0;
-    for (int row0 = task.row_begin; row0 < task.row_end; row0 += rpu, ++it) {
-      const int nrows = min(rpu, task.row_end - row0);
-      const int slot = it % sp.n_slots;
-      const uint32_t phase = (uint32_t)(it / sp.n_slots) & 1u;
-      mbar_wait(&sm.empty[slot], phase ^ 1u);  // passes at once on the first lap
-      const uint32_t bytes = (uint32_t)nrows * (uint32_t)m * 4u;
-      sm.slot_desc[slot].x = task.mat; sm.slot_desc[slot].y = row0;
-      sm.slot_desc[slot].z = nrows; sm.slot_desc[slot].w = rot;
-      mbar_arrive(&sm.desc[slot]);
-      if (FUSE) {
-        mbar_arrive_expect_tx(&sm.full[slot], 2u * bytes);
-        bulk_g2s(sm.ring + (size_t)slot * sp.slot_bytes, mi.g + (size_t)row0 * m, bytes, &sm.full[slot]);
-        bulk_g2s(sm.ring + (size_t)slot * sp.slot_bytes + bytes, mi.e + (size_t)row0 * m, bytes, &sm.full[slot]);
-      } else {
-        mbar_arrive_expect_tx(&sm.full[slot], bytes);
-        bulk_g2s(sm.ring + (size_t)slot * sp.slot_bytes, mi.base + (size_t)row0 * m, bytes, &sm.full[slot]);
-      }
-      rot = (rot + sub_per_unit) % kConsumerWarps;
     }
     t = t_next;
     if (t < sp.n_tasks) task = sp.tasks[t];  // one round trip, covered by the slots already in flight
@@ -523,7 +550,7 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
   pdl_wait();
   if (sp.vec_mode) stream_vec_side_job(sp, ps);
   if (sp.n_direct) direct_p_from_m<R, FUSE>(pl, ps, sp, q_mem, p_mem, q_div);
-  int cur_mat = -1, m = 0, r = 0, pitch = 0;
+  int cur_mat = -1, cur_chunk = 0, m = 0, ld = 0, col0 = 0, r = 0, pitch = 0;  // m: columns per pass (row length in a slot)
   unsigned pphase = 0;  // bit s: parity of the partial barrier of slot s
   float* P = nullptr;
   float* Mw = nullptr;  // FUSE: the send buffer M is written to
@@ -544,15 +571,17 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
     if (u_n < 0) {  // Q unit (uniform over the consumer warps: every warp visits every unit)
       if (dbg) c0 = clock64();
       const StreamSmem::MatInfo mi = mat_info(pl, ps, sm, q_mem, u_mat);
-      if (u_mat != cur_mat) {
+      const int chunk = (u_w & kQFlagChunk1) ? 1 : 0;
+      if (u_mat != cur_mat || chunk != cur_chunk) {
         P = p_mem + pl.mats[u_mat].p_off;  // in flight while the Q data lands
         Mw = const_cast<float*>(mi.base);
-        m = mi.m; r = mi.r; pitch = q_pitch(m, R);
+        ld = mi.m; m = ld / mi.nchunk; col0 = chunk * m; r = mi.r; pitch = q_pitch(m, R);
         cur_mat = u_mat;
-        consumer_sync();  // everyone is done with the previous matrix' Q
+        cur_chunk = chunk;
+        consumer_sync();  // everyone is done with the previous Q
       }
       mbar_wait(&sm.full[slot], phase);
-      consume_q_unit<R>(sm.qs, base, mi.q, (u_w & kQFlagBulk) != 0, u_a, -u_n, m, r, pitch, q_div);
+      consume_q_unit<R>(sm.qs, base, mi.q + (size_t)col0 * r, (u_w & kQFlagBulk) != 0, u_a, -u_n, m, r, pitch, q_div);
       consumer_sync();
       if (lane == 0) mbar_arrive(&sm.empty[slot]);
       if (dbg) { d_q += clock64() - c0; ++d_sw; }
@@ -571,7 +600,8 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
     const int nitems = nsub * cs;
     // Every warp arrives on every unit, with or without an item: that keeps any slot's barriers within one lap of
     // every warp (a warp that skipped arrivals could find a slot two laps ahead and mis-read the parity).
-    const int j0 = (warp - u_w % kConsumerWarps + kConsumerWarps) % kConsumerWarps;
+    const int j0 = (warp - (u_w & 0xff) % kConsumerWarps + kConsumerWarps) % kConsumerWarps;
+    const bool accumulate = (u_w >> 8) != 0;  // second column half: add to what this lane stored in the first pass
     if (j0 >= nitems && cs == 1) {
       if (lane == 0) mbar_arrive(&sm.empty[slot]);
       continue;
@@ -604,7 +634,7 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
           for (int a = 0; a < ROWS; ++a) {
             const float4 e = *reinterpret_cast<const float4*>(rowp[a] + (size_t)u_n * m + 4 * k);
             x[a].x += e.x; x[a].y += e.y; x[a].z += e.z; x[a].w += e.w;
-            if (a < nr) st_stream4(Mw + (size_t)(u_a + rbase + a) * m + 4 * k, x[a]);
+            if (a < nr) st_stream4(Mw + (size_t)(u_a + rbase + a) * ld + col0 + 4 * k, x[a]);
           }
         }
 #pragma unroll
@@ -632,7 +662,10 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
           const int idx = lane / LPV;
           const int a = g + idx / R, c = idx % R;
           if (cs == 1) {
-            if (a < nr && c < r) st_out(P + (size_t)(u_a + rbase + a) * r + c, tot, sp.out_mc != 0);
+            if (a < nr && c < r) {
+              float* dst = P + (size_t)(u_a + rbase + a) * r + c;
+              if (accumulate) *dst = *dst + tot; else st_out(dst, tot, sp.out_mc != 0);
+            }
           } else {
             sm.part[(slot * kSplitItems + j) * 32 + g * R + idx] = tot;
           }
@@ -643,14 +676,17 @@ k_p_from_m_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
       __syncwarp();
       if (lane == 0) mbar_arrive(&sm.pbar[slot]);
       for (int sub = 0; sub < nsub; ++sub) {
-        if (warp != (u_w + sub * cs + cs - 1) % kConsumerWarps) continue;
+        if (warp != ((u_w & 0xff) + sub * cs + cs - 1) % kConsumerWarps) continue;
         mbar_wait(&sm.pbar[slot], (pphase >> slot) & 1u);
         if (lane < ROWS * R) {
           const float* pp = sm.part + (slot * kSplitItems + sub * cs) * 32 + lane;
           float t = pp[0];
           for (int sl = 1; sl < cs; ++sl) t += pp[sl * 32];
           const int a = lane / R, c = lane % R;
-          if (sub * ROWS + a < u_n && c < r) st_out(P + (size_t)(u_a + sub * ROWS + a) * r + c, t, sp.out_mc != 0);
+          if (sub * ROWS + a < u_n && c < r) {
+            float* dst = P + (size_t)(u_a + sub * ROWS + a) * r + c;
+            if (accumulate) *dst = *dst + t; else st_out(dst, t, sp.out_mc != 0);
+          }
         }
       }
       pphase ^= 1u << slot;
@@ -688,7 +724,7 @@ k_finalize_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
   pdl_wait();
   if (sp.vec_mode) stream_vec_side_job(sp, ps);
   if (sp.n_direct) direct_finalize<R>(pl, ps, sp, p_mem, q_mem, world);
-  int cur_mat = -1, m = 0, r = 0, pitch = 0;
+  int cur_mat = -1, cur_chunk = 0, m = 0, ld = 0, col0 = 0, r = 0, pitch = 0;
   const float* P = nullptr;
   float* Out = nullptr;
   float* Mem = nullptr;
@@ -702,16 +738,18 @@ k_finalize_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
     const float* base = reinterpret_cast<const float*>(sm.ring + (size_t)slot * sp.slot_bytes);
     if (u_n < 0) {  // Q unit
       const StreamSmem::MatInfo mi = mat_info(pl, ps, sm, q_mem, u_mat);
-      if (u_mat != cur_mat) {
+      const int chunk = (u_w & kQFlagChunk1) ? 1 : 0;
+      if (u_mat != cur_mat || chunk != cur_chunk) {
         P = p_mem + pl.mats[u_mat].p_off;  // these three loads are in flight while the Q data lands
         Out = ps.out[u_mat];
         Mem = ps.mem[u_mat];
-        m = mi.m; r = mi.r; pitch = q_pitch(m, R);
+        ld = mi.m; m = ld / mi.nchunk; col0 = chunk * m; r = mi.r; pitch = q_pitch(m, R);
         cur_mat = u_mat;
+        cur_chunk = chunk;
         consumer_sync();
       }
       mbar_wait(&sm.full[slot], phase);
-      consume_q_unit<R>(sm.qs, base, mi.q, (u_w & kQFlagBulk) != 0, u_a, -u_n, m, r, pitch, world);
+      consume_q_unit<R>(sm.qs, base, mi.q + (size_t)col0 * r, (u_w & kQFlagBulk) != 0, u_a, -u_n, m, r, pitch, world);
       consumer_sync();
       if (lane == 0) mbar_arrive(&sm.empty[slot]);
       continue;
@@ -723,7 +761,7 @@ k_finalize_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
     int cs = 1;
     while (nsub * cs < kConsumerWarps && cs < 8) cs <<= 1;
     const int nitems = nsub * cs;
-    const int j0 = (warp - u_w % kConsumerWarps + kConsumerWarps) % kConsumerWarps;
+    const int j0 = (warp - (u_w & 0xff) % kConsumerWarps + kConsumerWarps) % kConsumerWarps;
     if (j0 >= nitems) {  // see k_p_from_m_stream
       if (lane == 0) mbar_arrive(&sm.empty[slot]);
       continue;
@@ -764,7 +802,7 @@ k_finalize_stream(DevPlan pl, PtrSlot ps, StreamPlan sp, const float* __restrict
               o.z = fmaf(p[a][c], q[c].z, o.z);
               o.w = fmaf(p[a][c], q[c].w, o.w);
             }
-            const size_t g = (size_t)(u_a + rbase + a) * m + 4 * k;
+            const size_t g = (size_t)(u_a + rbase + a) * ld + col0 + 4 * k;
             st_stream4(Out + g, o);
             st_stream4(Mem + g, make_float4(x.x - o.x, x.y - o.y, x.z - o.z, x.w - o.w));
           }

@@ -125,6 +125,9 @@ SHAPE_SETS = {
     "transformer_slice": [(512, 768), (768,), (768, 768), (768,), (3072, 768), (3072,), (768, 3072), (2, 768), (2,)],
     "tall": [(30522, 64), (64,), (4099, 132), (1,)],
     "wide_chunked": [(9, 25088), (9,), (40, 30000), (3,), (70, 13001), (2,), (300, 8200), (300,)],
+    # wide matrices whose Q does not fit the streamed kernels' stage in one piece: streamed in two column halves
+    # (4096 and 8200 columns at rank 8 / 4, 3072 at rank 16), the second pass adding to the first pass' P
+    "column_halves": [(96, 4096), (5,), (1024, 3072), (3072,), (300, 8200), (3,), (520, 6144), (2,)],
     "conv": [(128, 64, 3, 3), (128,), (256, 128, 1, 1), (256,), (512, 512, 3, 3), (512,), (1000, 512), (1000,)],
 }
 
@@ -134,7 +137,7 @@ SHAPE_SETS = {
 def test_matches_oracle_single_step(setname, rank):
     from tests.gpu_common import run_pair
 
-    if setname in ("tall", "wide_chunked", "conv") and rank in (3, 32):
+    if setname in ("tall", "wide_chunked", "conv", "column_halves") and rank in (3, 32):
         pytest.skip("covered by the other ranks; keeps the suite short")
     from tests.gpu_common import within_tolerance
 
@@ -329,7 +332,7 @@ def test_full_size_distilbert_properties(rank):
     assert all(torch.equal(a, b) for a, b in zip(gout, gout2)) and all(torch.equal(a, b) for a, b in zip(mem, mem2))
 
 
-@pytest.mark.parametrize("setname", ["transformer_slice", "odd_columns", "wide_chunked"])
+@pytest.mark.parametrize("setname", ["transformer_slice", "odd_columns", "wide_chunked", "column_halves"])
 def test_reduce_fused_matches_add_then_reduce(setname):
     """reduce_fused(grads, memories, send) == (send = g + e; reduce(send, grads, memories)) on the GPU, both
     through the streamed kernels (aligned transformer shapes) and the direct ones (odd / wide shapes)."""
