@@ -94,6 +94,27 @@ class PowerSGDReducer(Reducer):
         torch.manual_seed(self.rng.randint(1_000_000_000))
         vector.data[:] = torch.randn(*vector.shape, device=self.device)
 
+    def _draw_queries(self, queries):
+        """One round of reducer.py:104-111: a fresh seed and a fresh randn per matrix, in matrix order.
+
+        Upstream reseeds the GLOBAL generators once per matrix (``torch.manual_seed``, ~80 us a call: with
+        ``reuse_query=False`` that alone is 3-4 ms per step on DistilBERT).  Only the last of those reseeds is observable
+        afterwards, so all matrices but the last draw from a private generator seeded with the same seed -- the same
+        Philox / mt19937 stream, hence the same Q -- and the last one goes through ``_set_random`` as upstream does,
+        which leaves the global CPU and CUDA generators exactly where upstream leaves them."""
+        if "_set_random" in self.__dict__:  # instrumented by a test / caller: keep handing every matrix to it
+            for q in queries:
+                self._set_random(q)
+            return
+        gen = self.__dict__.get("_private_gen")
+        if gen is None:
+            gen = self._private_gen = torch.Generator(device=self.device)
+        for q in queries[:-1]:
+            gen.manual_seed(int(self.rng.randint(1_000_000_000)))
+            q.data[:] = torch.randn(*q.shape, device=self.device, generator=gen)
+        if queries:
+            self._set_random(queries[-1])
+
     # ---------------------------------------------------------------------------------------
     def _plan_for(self, grad_in, mats, vecs):
         key = tuple(tuple(t.shape) for t in grad_in)
@@ -186,9 +207,8 @@ class PowerSGDReducer(Reducer):
 
             # reducer.py:101-111
             if not (self.reuse_query and not mem_uninitialized):
-                for info in plan.mats:
-                    q = self.q_memory[info["q_off"] : info["q_off"] + info["m"] * info["r"]].view(info["m"], info["r"])
-                    self._set_random(q)
+                self._draw_queries([self.q_memory[info["q_off"] : info["q_off"] + info["m"] * info["r"]].view(info["m"], info["r"])
+                                    for info in plan.mats])
 
             if fused:
                 plan.set_ptrs(mats, [grad_out[i] for i in mat_idx], [memory_out[i] for i in mat_idx],
