@@ -65,6 +65,27 @@ def test_peer_allreduce_entry_points_validate_before_touching_the_gpu(lib):
                                       ctypes.c_float(1.0), 0, None, 0, None) != 0 and b"blocks_done" in lib.psgd_last_error()
 
 
+def test_peer_handles_validate_before_touching_the_gpu(lib):
+    """psgd_peer_create / psgd_peer_create_push: geometry errors are reported, nothing is launched."""
+    one = _lib.ptr_array([16, 32])
+    h = ctypes.c_void_p()
+    mk = lambda world, rank, mode, mc=16: lib.psgd_peer_create(world, rank, 0, one, one, ctypes.c_void_p(mc), one, one,
+                                                              ctypes.c_void_p(mc), 256, mode, ctypes.byref(h))
+    assert mk(1, 0, 2) != 0 and b"world size" in lib.psgd_last_error()
+    assert mk(2, 2, 2) != 0 and b"rank" in lib.psgd_last_error()
+    assert mk(2, 0, 7) != 0 and b"mode" in lib.psgd_last_error()
+    assert mk(2, 0, 1, mc=0) != 0 and b"multicast" in lib.psgd_last_error()
+    push = lambda stride, mc=16: lib.psgd_peer_create_push(2, 0, 0, ctypes.c_void_p(16), ctypes.c_void_p(mc), stride, one,
+                                                           ctypes.c_void_p(16), ctypes.c_void_p(16), 8, one, 256,
+                                                           ctypes.byref(h))
+    assert push(6) != 0 and b"stride" in lib.psgd_last_error()
+    assert push(8, mc=0) != 0 and b"multicast" in lib.psgd_last_error()
+    assert lib.psgd_orthogonalize_peer(None, None, None, None, None) != 0
+    assert lib.psgd_finalize_peer(None, None, None, None, None, None) != 0
+    assert lib.psgd_p_from_m_push(None, None, None, 0, 1, 0, None) != 0
+    assert lib.psgd_peer_destroy(None) == 0
+
+
 def split(shapes):
     mats = [(s[0], int(np.prod(s[1:]))) for s in shapes if len(s) > 1]
     vecs = [int(np.prod(s)) if len(s) else 1 for s in shapes if len(s) <= 1]

@@ -147,6 +147,20 @@ def test_matches_oracle_single_step(setname, rank):
     assert res["p"] < TOL and res["q"] < TOL, res
 
 
+@pytest.mark.parametrize("rank", [16, 32])
+@pytest.mark.parametrize("setname", ["transformer_slice", "odd_columns", "column_halves"])
+def test_tensor_pipe_variants_match_oracle(monkeypatch, setname, rank):
+    """The 3 x TF32 mma.sync kernels of csrc/psgd_tc.cuh (K1, K3, K4 at ranks 16 / 32).  They are off by default
+    (measured slower than the FFMA kernels) but kept and kept correct: same 1e-5 gate.  Plain
+    TF32 would miss it by two orders of magnitude; the split passes."""
+    from tests.gpu_common import run_pair, within_tolerance
+
+    monkeypatch.setenv("PSGD_TC", "7")
+    res = run_pair(SHAPE_SETS[setname], rank, steps=1)[0]
+    assert within_tolerance(res) == [], res
+    assert res["p"] < TOL and res["q"] < TOL, res
+
+
 @pytest.mark.parametrize("reuse", [True, False])
 def test_three_steps_with_error_feedback(reuse):
     from tests.gpu_common import run_pair
