@@ -228,7 +228,10 @@ void build_stream_tasks(const psgd_plan* p, int rows_per_sub, int slot_bytes, st
   });
 
   const long long div0 = 2LL * p->stream_grid * env_ll("PSGD_GSS_DIV", 1);
-  const long long min_units0 = std::max<long long>(1, env_ll("PSGD_GSS_MIN_UNITS", 2));
+  // small sets (under ~1 MB per CTA, e.g. ResNet-18: 0.3 MB) get longer tasks: with only a handful of ring units per
+  // CTA every extra task is an extra Q stage the consumers wait for (ResNet-18 r=2: 104 -> 95 us)
+  const long long min_units_dflt = (total / std::max(1, p->stream_grid) < (1 << 20)) ? 4 : 2;
+  const long long min_units0 = std::max<long long>(1, env_ll("PSGD_GSS_MIN_UNITS", min_units_dflt));
   // The end of the schedule lies inside the last (largest) matrix, where a finer cut costs no extra Q stage: a CTA's
   // consecutive tasks are then of the same matrix.  Elsewhere finer tasks mean more matrix switches per CTA.
   // (measured: DistilBERT r=4 step 236.8 -> 232.3 us, r=8 280.4 -> 274.5 us; tasks under ~48 KB cost ResNet-50, whose
