@@ -438,3 +438,33 @@ def test_timing_and_launch_counter():
     tm = plan.timing_read()
     assert all(cnt == 1 and ms > 0 for name, (ms, cnt) in tm.items() if name != "q_reduce")
     assert tm["q_reduce"][1] == 0
+
+
+def test_results_are_complete_when_an_event_after_reduce_fires():
+    """The kernels of a step are launched with programmatic stream serialisation (each lets its successor start
+    early and the successor waits in-kernel).  That must stay invisible to the caller: an event recorded right after
+    reduce() fires only when grad_out and memory_out are complete, so a copy on another stream that waits for the
+    event sees the final values.  Repeated, with new inputs every time."""
+    from network_distributed_pytorch_b200.reducer import PowerSGDReducer
+
+    dev = torch.device("cuda", 0)
+    shapes = SHAPE_SETS["transformer_slice"]
+    red = PowerSGDReducer(714, dev, 0, True, 4)
+    gin = [torch.randn(s, device=dev) for s in shapes]
+    gout = [torch.zeros(s, device=dev) for s in shapes]
+    mem = [torch.zeros(s, device=dev) for s in shapes]
+    side = torch.cuda.Stream(dev)
+    snap = [torch.empty_like(t) for t in gout + mem]
+    for it in range(40):
+        for t in gin:
+            t.normal_()
+        red.reduce(gin, gout, mem)
+        ev = torch.cuda.Event()
+        ev.record()
+        with torch.cuda.stream(side):
+            side.wait_event(ev)
+            for d, s in zip(snap, gout + mem):
+                d.copy_(s, non_blocking=True)
+        torch.cuda.synchronize()
+        for d, s in zip(snap, gout + mem):
+            assert torch.equal(d, s), it
