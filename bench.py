@@ -719,6 +719,33 @@ def run_b200(args):
         del out_b, gouts2
         barrier()
 
+    # ---- the same step replayed from a CUDA graph (PowerSGDReducer.capture): host time per step ----------
+    graph_leg = None
+    if world == 1 and not args.no_phase_timing and args.extra_power_iterations >= 0 and not args.no_reuse_query:
+        try:
+            cap = red.capture(gin, gout, mem)
+            for _ in range(3):
+                cap.replay()
+            n_g = min(K, 50)
+            g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            barrier()
+            g0.record()
+            h0 = time.perf_counter()
+            for _ in range(n_g):
+                cap.replay()
+            g_host = (time.perf_counter() - h0) / n_g * 1e6
+            g1.record()
+            barrier()
+            graph_leg = {"ms_per_step": g0.elapsed_time(g1) / n_g, "host_issue_us_per_step": round(g_host, 1), "steps": n_g,
+                         "what": "PowerSGDReducer.capture(): the four kernels of a step with their programmatic dependencies "
+                                 "as one CUDA graph, replayed"}
+            del cap
+        except Exception as exc:  # noqa: BLE001 -- a diagnostic leg
+            graph_leg = {"unavailable": f"{type(exc).__name__}: {exc}"[:300]}
+        in_flat.normal_(generator=gen)
+        mem_flat.zero_()
+        barrier()
+
     # ---- e2e: gradients start in pinned host memory, grad_out is read back ------------------------
     # Three streams and two device buffer sets: the H2D copy of step k+1 and the D2H copy of step k-1 run on
     # the two copy engines while step k reduces, exactly as a host-resident caller would pipeline the
@@ -915,7 +942,7 @@ def run_b200(args):
         "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": int(launches),
         "allreduce": allreduce_kind, "parity": parity,
         "torch_gpu_baseline": torch_base, "cpu_baseline_gloo2": cpu_gloo2, "dense": dense, "configs": configs,
-        "host_issue_us_per_step_fresh_ptrs": fresh,
+        "host_issue_us_per_step_fresh_ptrs": fresh, "graph_replay": graph_leg,
         "clocks": clocks, "phases": phase_report,
         "phases_note": "per-phase event brackets measured in a separate pass (they add ~13 % to the step and keep the kernels from overlapping head to tail); "
                        "inside the timed region only finalize is bracketed, on every 4th step",
