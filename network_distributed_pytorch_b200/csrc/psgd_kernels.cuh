@@ -802,7 +802,11 @@ k_q_from_mt(DevPlan pl, PtrSlot ps, const float* __restrict__ p_mem, float* __re
         sum.x += v.x; sum.y += v.y; sum.z += v.z; sum.w += v.w;
       }
       if (q_mc) {  // pushed into every rank's receive buffer (q_mem is a multicast address)
-        mm_st1(dst + 4 * f, sum.x); mm_st1(dst + 4 * f + 1, sum.y); mm_st1(dst + 4 * f + 2, sum.z); mm_st1(dst + 4 * f + 3, sum.w);
+        if ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+          mm_st4(dst + 4 * f, sum);
+        } else {
+          mm_st1(dst + 4 * f, sum.x); mm_st1(dst + 4 * f + 1, sum.y); mm_st1(dst + 4 * f + 2, sum.z); mm_st1(dst + 4 * f + 3, sum.w);
+        }
       } else {
         dst[4 * f] = sum.x; dst[4 * f + 1] = sum.y; dst[4 * f + 2] = sum.z; dst[4 * f + 3] = sum.w;
       }
