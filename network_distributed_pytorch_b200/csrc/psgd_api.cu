@@ -230,7 +230,10 @@ void build_stream_tasks(const psgd_plan* p, int rows_per_sub, int slot_bytes, st
   const long long div0 = 2LL * p->stream_grid * env_ll("PSGD_GSS_DIV", 1);
   // small sets (under ~1 MB per CTA, e.g. ResNet-18: 0.3 MB) get longer tasks: with only a handful of ring units per
   // CTA every extra task is an extra Q stage the consumers wait for (ResNet-18 r=2: 104 -> 95 us)
-  const long long min_units_dflt = (total / std::max(1, p->stream_grid) < (1 << 20)) ? 4 : 2;
+  // (measured, ResNet-18 r=2, 0.3 MB per CTA: floor 2 -> 104 us, 4 -> 95, 8 -> 90, 12 -> 101; ResNet-50, 0.7 MB per CTA:
+  // 4 -> 118, 6 -> 126, 8 -> 123)
+  const long long per_cta = total / std::max(1, p->stream_grid);
+  const long long min_units_dflt = per_cta < (512 << 10) ? 8 : per_cta < (1 << 20) ? 4 : 2;
   const long long min_units0 = std::max<long long>(1, env_ll("PSGD_GSS_MIN_UNITS", min_units_dflt));
   // The end of the schedule lies inside the last (largest) matrix, where a finer cut costs no extra Q stage: a CTA's
   // consecutive tasks are then of the same matrix.  Elsewhere finer tasks mean more matrix switches per CTA.
@@ -414,7 +417,11 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
 
   const long long t1_bytes = env_ll("PSGD_T1_BYTES", 128 * 1024);
   const long long t4_bytes = env_ll("PSGD_T4_BYTES", 96 * 1024);
-  const long long t3_bytes = env_ll("PSGD_T3_BYTES", 256 * 1024);
+  // K3 tiles: 256 KB of M each; half that for very small sets (under 0.5 MB per SM), whose few tiles per SM otherwise
+  // leave the tail unbalanced (ResNet-18 r=2: 90 -> 85 us; ResNet-50 at 0.7 MB per SM loses 3 us with it)
+  long long total_bytes = 0;
+  for (int i = 0; i < n_mat; ++i) total_bytes += (long long)n[i] * m[i] * 4;
+  const long long t3_bytes = env_ll("PSGD_T3_BYTES", (total_bytes / 148 < (512 << 10)) ? 128 * 1024 : 256 * 1024);
   const long long t3_maxblk = env_ll("PSGD_T3_MAXBLK", 48);
   const int cgw_cap = (int)std::min<long long>(env_ll("PSGD_T3_CGW", 64), kThreads3);
 
