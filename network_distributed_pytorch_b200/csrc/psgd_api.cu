@@ -81,7 +81,7 @@ struct psgd_plan {
   bool pdl = true;              // programmatic dependent launch between the kernels of a step (PSGD_PDL)
   bool orth_merge = true;       // small matrices ride on the tall launch (PSGD_ORTH_MERGE)
   int orth_merge_max_ctas = 96;
-  bool orth16_attr = false;
+  bool orth16_attr = false, orth16_attr_peer = false;  // 16-CTA clusters allowed on the K2 kernel of this plan's R
   int *d_orth_small = nullptr, *d_orth_tall = nullptr, *d_orth_generic = nullptr;
   size_t smem1 = 0, smem3 = 0, smem4 = 0;
   // streamed (bulk-copy ring) path for K1 / K4
@@ -173,6 +173,44 @@ struct psgd_peer {
 };
 
 namespace {
+
+// can this device hold a 16-CTA cluster of the register-resident Gram-Schmidt kernel (one CTA per SM)?
+bool orth_cluster16_ok(int R, int device) {
+  const void* fn = nullptr;
+  switch (R) {
+    case 1: fn = (const void*)k_orth_tall<1, 4>; break;
+    case 2: fn = (const void*)k_orth_tall<2, 4>; break;
+    case 4: fn = (const void*)k_orth_tall<4, 4>; break;
+    case 8: fn = (const void*)k_orth_tall<8, 4>; break;
+    default: return false;
+  }
+  int cur = -1;
+  cudaGetDevice(&cur);
+  struct Restore {
+    int d;
+    ~Restore() { if (d >= 0) cudaSetDevice(d); }
+  } restore{cur};
+  if (cudaSetDevice(device) != cudaSuccess ||
+      cudaFuncSetAttribute(fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  cudaLaunchConfig_t cfg{};
+  cfg.gridDim = dim3(kOrthClusterMax);
+  cfg.blockDim = dim3(orth_threads(R));
+  cudaLaunchAttribute at{};
+  at.id = cudaLaunchAttributeClusterDimension;
+  at.val.clusterDim.x = kOrthClusterMax;
+  at.val.clusterDim.y = at.val.clusterDim.z = 1;
+  cfg.attrs = &at;
+  cfg.numAttrs = 1;
+  int n = 0;
+  if (cudaOccupancyMaxActiveClusters(&n, fn, &cfg) != cudaSuccess) {
+    cudaGetLastError();
+    return false;
+  }
+  return n >= 1;
+}
 
 DevPlan dev_plan(const psgd_plan* p) {
   DevPlan d;
@@ -618,7 +656,12 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
 
   {  // K2 routing: register-resident single CTA, register-resident cluster, or generic cluster
     const int rpt = 4;  // rows per thread of the register-resident Gram-Schmidt kernels (1024 threads, 512 at R = 16)
-    p->orth_tall_cluster = (R == 16) ? kOrthClusterMax : kOrthCluster;  // R = 16: 512 threads x 4 rows per CTA
+    // A tall matrix is spread over a cluster of 16 CTAs: half the rows, and so half the warps, of 8 CTAs -- a step is
+    // bound by the instructions a CTA issues (DistilBERT r=4 234 -> 232 us, r=8 276 -> 271; K2's embedding cluster
+    // 10.4 -> 8.1 us).  8 where the device cannot place such a cluster (R = 16: 512 threads x 4 rows, 16 CTAs as before).
+    p->orth_tall_cluster = kOrthCluster;
+    if (R == 16 || (env_ll("PSGD_ORTH_TALL_CLUSTER", 16) >= 16 && (device < 0 || orth_cluster16_ok(R, device))))
+      p->orth_tall_cluster = kOrthClusterMax;
     p->orth_merge = env_ll("PSGD_ORTH_MERGE", 1) != 0;
     p->pdl = env_ll("PSGD_PDL", 1) != 0;
     // measured: pays at R >= 8 (twice the FMAs per byte: DistilBERT r=8 step 291 -> 284 us), costs 1-3 % at R <= 4
@@ -1121,7 +1164,11 @@ static int orth_impl(psgd_plan* p, float* p_mem, float n_workers, psgd_stream st
     if (pass == 0) {
       const int* d_small = p->d_orth_small;
       if (p->R <= 8) {
-        DISPATCH_R8(p->R, { CU(launch_ex(k_orth_tall<RR, 4>, grid, dim3(orth_threads(p->R)), 0, s, csz, p->pdl, dp, d_ids, n_tall, d_small, n_ride, p_mem, n_workers)); });
+        DISPATCH_R8(p->R, {
+          if (csz > 8 && !p->orth16_attr) CU(cudaFuncSetAttribute((const void*)k_orth_tall<RR, 4>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+          p->orth16_attr = true;
+          CU(launch_ex(k_orth_tall<RR, 4>, grid, dim3(orth_threads(p->R)), 0, s, csz, p->pdl, dp, d_ids, n_tall, d_small, n_ride, p_mem, n_workers));
+        });
       } else {
         if (!p->orth16_attr) CU(cudaFuncSetAttribute((const void*)k_orth_tall<16, 4>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
         p->orth16_attr = true;
@@ -1514,9 +1561,14 @@ int psgd_orthogonalize_peer(psgd_plan* p, psgd_peer* peer, float* p_mem, float* 
     const int n_ride = merged ? n_small : 0;
     const dim3 grid((unsigned)(n_tall + (n_ride + n_flat_ctas + tcs - 1) / tcs) * tcs);
     if (p->R <= 8) {
-      DISPATCH_R8(p->R, { CU(launch_ex(k_orth_tall_peer<RR, 4>, grid, dim3(orth_threads(p->R)), 0, s, tcs, p->pdl, dp, (const int*)p->d_orth_tall, n_tall, (const int*)p->d_orth_small, n_ride, p_mem, world, pm, pf)); });
+      DISPATCH_R8(p->R, {
+        if (tcs > 8 && !p->orth16_attr_peer) CU(cudaFuncSetAttribute((const void*)k_orth_tall_peer<RR, 4>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        p->orth16_attr_peer = true;
+        CU(launch_ex(k_orth_tall_peer<RR, 4>, grid, dim3(orth_threads(p->R)), 0, s, tcs, p->pdl, dp, (const int*)p->d_orth_tall, n_tall, (const int*)p->d_orth_small, n_ride, p_mem, world, pm, pf));
+      });
     } else {
-      CU(cudaFuncSetAttribute((const void*)k_orth_tall_peer<16, 4>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+      if (!p->orth16_attr_peer) CU(cudaFuncSetAttribute((const void*)k_orth_tall_peer<16, 4>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+      p->orth16_attr_peer = true;
       CU(launch_ex(k_orth_tall_peer<16, 4>, grid, dim3(orth_threads(p->R)), 0, s, tcs, p->pdl, dp, (const int*)p->d_orth_tall, n_tall, (const int*)p->d_orth_small, n_ride, p_mem, world, pm, pf));
     }
     if (check_launch("k_orth_tall_peer")) return 1;
@@ -1959,3 +2011,9 @@ extern "C" int psgd_q_from_mt_noalloc(const float* mat, const float* p_hat, floa
   return check_launch("k_q_reduce_single");
 }
 
+
+#ifdef PSGD_ORTH_TS
+extern "C" int psgd_debug_orth_ts(unsigned long long* out) {
+  return (int)cudaMemcpyFromSymbol(out, psgd::g_orth_ts, sizeof(unsigned long long) * 64 * 12);
+}
+#endif

@@ -270,22 +270,46 @@ __device__ __forceinline__ void orth_body(float* __restrict__ P, int n, int r, f
   }
 }
 
+#ifdef PSGD_ORTH_TS
+__device__ unsigned long long g_orth_ts[64][12];
+__device__ __forceinline__ void orth_ts(int slot) {
+  if (threadIdx.x == 0 && blockIdx.x < 64) {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    g_orth_ts[blockIdx.x][slot] = t;
+  }
+}
+#define ORTH_TS(s) orth_ts(s)
+#else
+#define ORTH_TS(s)
+#endif
 // Register-resident variant: every thread keeps its (at most RPT) rows in registers for all r steps,
 // so P is read once and written once and a step costs one block (+ cluster) reduction.  csize == 1
 // runs a whole matrix in one CTA with block barriers only; csize > 1 spreads one tall matrix over a
 // thread-block cluster and exchanges the partials through distributed shared memory.  All sums are
 // formed in a fixed order (xor-shuffle trees, then CTA rank order), so results are deterministic.
 //   wsum: 32 * R floats, part: 2 * kOrthClusterMax * R floats, both 16-byte aligned shared memory
+//   cbar (csize > 1): two mbarriers (count 1), initialised and made known to the cluster by the caller (orth_cluster_init).
+// The cluster exchange of a step is one-way: warp 0 of every CTA sends its partial sums into every CTA's `part`
+// with st.async, which also counts the bytes on the receiver's mbarrier; a CTA goes on as soon as its own barrier has
+// seen all csize partials.  (A cluster-wide barrier after plain remote stores cost 1.05 us per step, twice the step
+// itself.)  `part` and the barriers alternate between two sets: a CTA that is one step ahead writes the other set, and
+// it cannot be two ahead because it needs this CTA's next partial first.
 // pm != nullptr: the rows are read "summed over all ranks" from symmetric memory (element offset sym_off of the
 // buffer pm describes: the SUM all-reduce of reducer.py:126 happens on load), the result goes to the local P.
 template <int R, int RPT>
 __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r, float world,
-                                            int crank, int csize, float* wsum, float* part,
+                                            int crank, int csize, float* wsum, float* part, uint64_t* cbar,
                                             const PeerLoad* pm = nullptr, long long sym_off = 0) {
   constexpr int LPV = 32 / R;  // lanes per value after a warp_fold<R>
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int nthr = blockDim.x, nwarp = nthr >> 5;
   const int per = (n + csize - 1) / csize;
+  // Only as many warps as the rows need stay: a step is bound by the instructions the CTA issues (fold, barrier, scale
+  // factors: the same for every warp, with or without rows), not by its arithmetic.  The others leave before the first
+  // barrier; block and cluster barriers count the threads that have not exited.
+  const int want = (((per + RPT - 1) / RPT) + 31) & ~31;
+  const int nthr = want < (int)blockDim.x ? want : (int)blockDim.x, nwarp = nthr >> 5;
+  if (tid >= nthr) return;
   const int lo = crank * per;
   const int hi = (lo + per < n) ? lo + per : n;
   auto cta_sync = [] { __syncthreads(); };
@@ -322,6 +346,7 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
 #pragma unroll
       for (int j = 0; j < R; ++j) v[k][j] *= inv_world;
   }
+  ORTH_TS(2);
 
   // For R <= 8 the step loop stays ROLLED: unrolled, the R steps are R copies of straight-line code that every warp runs exactly
   // once, and the kernel spent most of its time waiting for instruction fetches (ncu: stall_no_inst 42 % at R = 8,
@@ -351,19 +376,19 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
 #pragma unroll
         for (int j = 0; j < R; ++j) t[j] = (lane < nwarp) ? wsum[lane * R + j] : 0.f;
         const float w = warp_fold<R>(t, lane);
-        if ((lane % LPV) == 0) {
+        if (csize > 1) {
+          // one message per (value, destination CTA): it lands in the receiver's `part` and counts on its mbarrier.
+          // All LPV lanes of a group hold the group's value after the fold, so they share out the destinations.
           const int j = lane / LPV;
-          if (csize > 1) {
-            for (int dst = 0; dst < csize; ++dst) {
-              float* remote = cg::this_cluster().map_shared_rank(part, dst);
-              remote[(par * kOrthClusterMax + crank) * R + j] = w;
-            }
-          } else {
-            part[(par * kOrthClusterMax) * R + j] = w;
-          }
+          const uint32_t slot = smem_u32(part + (par * kOrthClusterMax + crank) * R + j), bar = smem_u32(&cbar[par]);
+          for (int dst = lane % LPV; dst < csize; dst += LPV)
+            st_async_f32(cluster_map_u32(slot, dst), w, cluster_map_u32(bar, dst));
+          if (lane == 0) mbar_arrive_expect_tx(&cbar[par], (uint32_t)csize * R * 4u);
+        } else if ((lane % LPV) == 0) {
+          part[(par * kOrthClusterMax) * R + lane / LPV] = w;
         }
       }
-      if (csize > 1) cg::this_cluster().sync(); else cta_sync();
+      if (csize > 1) mbar_wait_lite(&cbar[par], (uint32_t)(i >> 1) & 1u); else cta_sync();
       float tot[R];
 #pragma unroll
       for (int j = 0; j < R; ++j) tot[j] = 0.f;
@@ -392,6 +417,7 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
         }
       }
     }
+    ORTH_TS(3 + i);
 #pragma unroll
     for (int k = 0; k < RPT; ++k) {
       const float head = v[k][0];
@@ -424,19 +450,19 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
 #pragma unroll
         for (int j = 0; j < R; ++j) t[j] = (lane < nwarp) ? wsum[lane * R + j] : 0.f;
         const float w = warp_fold<R>(t, lane);
-        if ((lane % LPV) == 0) {
+        if (csize > 1) {
+          // one message per (value, destination CTA): it lands in the receiver's `part` and counts on its mbarrier.
+          // All LPV lanes of a group hold the group's value after the fold, so they share out the destinations.
           const int j = lane / LPV;
-          if (csize > 1) {
-            for (int dst = 0; dst < csize; ++dst) {
-              float* remote = cg::this_cluster().map_shared_rank(part, dst);
-              remote[(par * kOrthClusterMax + crank) * R + j] = w;
-            }
-          } else {
-            part[(par * kOrthClusterMax) * R + j] = w;
-          }
+          const uint32_t slot = smem_u32(part + (par * kOrthClusterMax + crank) * R + j), bar = smem_u32(&cbar[par]);
+          for (int dst = lane % LPV; dst < csize; dst += LPV)
+            st_async_f32(cluster_map_u32(slot, dst), w, cluster_map_u32(bar, dst));
+          if (lane == 0) mbar_arrive_expect_tx(&cbar[par], (uint32_t)csize * R * 4u);
+        } else if ((lane % LPV) == 0) {
+          part[(par * kOrthClusterMax) * R + lane / LPV] = w;
         }
       }
-      if (csize > 1) cg::this_cluster().sync(); else cta_sync();
+      if (csize > 1) mbar_wait_lite(&cbar[par], (uint32_t)(i >> 1) & 1u); else cta_sync();
       float tot[R];
 #pragma unroll
       for (int j = 0; j < R; ++j) tot[j] = 0.f;
@@ -482,6 +508,18 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
       }
     }
   }
+  ORTH_TS(11);
+}
+
+// the two exchange barriers of a cooperating cluster: initialised, then made known to all its CTAs before any of them
+// can send (all threads of all CTAs of the cluster call this; it does not depend on an earlier kernel)
+__device__ __forceinline__ void orth_cluster_init(uint64_t* cbar) {
+  if (threadIdx.x == 0) {
+    mbar_init(&cbar[0], 1);
+    mbar_init(&cbar[1], 1);
+    mbar_fence_init();
+  }
+  cg::this_cluster().sync();
 }
 
 // one CTA per "small" matrix (n <= blockDim * RPT)
@@ -494,7 +532,7 @@ k_orth_small(DevPlan pl, const int* __restrict__ ids, float* __restrict__ p_mem,
   const int mat = ids[blockIdx.x];
   const MatDesc md = pl.mats[mat];
   pdl_wait();
-  orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, 0, 1, wsum, part);
+  orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, 0, 1, wsum, part, nullptr);
 }
 
 // The flat <=1-D buffer travels behind P in the same symmetric buffer (reducer.py:131-133): CTAs past the matrices sum
@@ -534,7 +572,7 @@ k_orth_small_peer(DevPlan pl, const int* __restrict__ ids, int n_small, float* _
   if ((int)blockIdx.x < n_small) {
     const int mat = ids[blockIdx.x];
     const MatDesc md = pl.mats[mat];
-    orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, 0, 1, wsum, part, &pm, md.p_off);
+    orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, 0, 1, wsum, part, nullptr, &pm, md.p_off);
   } else if (pf.out) {
     peer_flat_job(pm, pf, (int)blockIdx.x - n_small);
   }
@@ -552,12 +590,16 @@ k_orth_tall(DevPlan pl, const int* __restrict__ ids, int n_tall, const int* __re
   cg::cluster_group cluster = cg::this_cluster();
   const int csize = (int)cluster.num_blocks();
   const int cl = blockIdx.x / csize;
+  __shared__ uint64_t cbar[2];
+  ORTH_TS(0);
   pdl_launch_dependents();
   if (cl < n_tall) {
     const int mat = ids[cl];
     const MatDesc md = pl.mats[mat];
+    orth_cluster_init(cbar);  // under the predecessor's tail
     pdl_wait();
-    orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, (int)cluster.block_rank(), csize, wsum, part);
+    ORTH_TS(1);
+    orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, (int)cluster.block_rank(), csize, wsum, part, cbar);
   } else {
     const int idx = (cl - n_tall) * csize + (int)cluster.block_rank();
     if (idx >= n_small) {
@@ -567,7 +609,8 @@ k_orth_tall(DevPlan pl, const int* __restrict__ ids, int n_tall, const int* __re
     const int mat = small_ids[idx];
     const MatDesc md = pl.mats[mat];
     pdl_wait();
-    orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, 0, 1, wsum, part);
+    ORTH_TS(1);
+    orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, 0, 1, wsum, part, nullptr);
   }
 }
 
@@ -581,19 +624,21 @@ k_orth_tall_peer(DevPlan pl, const int* __restrict__ ids, int n_tall, const int*
   cg::cluster_group cluster = cg::this_cluster();
   const int csize = (int)cluster.num_blocks();
   const int cl = blockIdx.x / csize;
+  __shared__ uint64_t cbar[2];
   pdl_launch_dependents();
+  if (cl < n_tall) orth_cluster_init(cbar);  // under the predecessor's tail
   pdl_wait();
   peer_barrier(pm, blockIdx.x == 0);
   if (cl < n_tall) {
     const int mat = ids[cl];
     const MatDesc md = pl.mats[mat];
-    orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, (int)cluster.block_rank(), csize, wsum, part, &pm, md.p_off);
+    orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, (int)cluster.block_rank(), csize, wsum, part, cbar, &pm, md.p_off);
   } else {
     const int idx = (cl - n_tall) * csize + (int)cluster.block_rank();
     if (idx < n_small) {
       const int mat = small_ids[idx];
       const MatDesc md = pl.mats[mat];
-      orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, 0, 1, wsum, part, &pm, md.p_off);
+      orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, 0, 1, wsum, part, nullptr, &pm, md.p_off);
     } else if (pf.out) {
       peer_flat_job(pm, pf, idx - n_small);
     }
