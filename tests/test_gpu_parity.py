@@ -419,6 +419,37 @@ def test_orthogonalize_module_function():
         assert rel_err(b.cpu().numpy(), a.numpy()) < TOL, (n, r)
 
 
+@pytest.mark.parametrize("rank", [1, 3, 4, 8, 16])
+def test_orthogonalize_routes_by_row_count(rank):
+    """K2 alone (plan.orthogonalize on a random P) at the row counts where its routing changes: own CTA with only the
+    warps that own rows (n <= 4096), 16-CTA cluster with the one-way st.async exchange (up to 65536 rows; ragged last
+    CTA, CTAs without rows), generic global-memory cluster kernel above -- against the oracle's modified Gram-Schmidt
+    (reducer.py:180-191), clipped ranks (r < R) included."""
+    from network_distributed_pytorch_b200.engine import CudaEngine
+    from oracle.powersgd_oracle import gram_schmidt_inplace
+
+    dev = torch.device("cuda", 0)
+    eng = CudaEngine(dev)
+    rows = [1, 33, 768, 4096, 4097, 8191, 30522, 40000, 65536, 65537]
+    shapes = [(n, 16) for n in rows]
+    plan = eng.make_plan(shapes, rank, [16])
+    torch.manual_seed(rank)
+    p = torch.randn(plan.p_elems, device=dev)
+    want = p.cpu().clone()
+    tensors = [torch.zeros(s, device=dev) for s in shapes]
+    plan.set_ptrs(tensors, [torch.zeros_like(t) for t in tensors], [torch.zeros_like(t) for t in tensors],
+                  [torch.zeros(16, device=dev)], [torch.zeros(16, device=dev)])
+    plan.orthogonalize(p, 1)
+    torch.cuda.synchronize()
+    got = p.cpu()
+    for info in plan.mats:
+        n, r, off = info["n"], info["r"], info["p_off"]
+        ref = want[off : off + n * r].view(n, r).clone()
+        gram_schmidt_inplace(ref)
+        err = rel_err(got[off : off + n * r].view(n, r).numpy(), ref.numpy())
+        assert err < TOL, (n, r, err)
+
+
 def test_timing_and_launch_counter():
     from network_distributed_pytorch_b200.engine import CudaEngine
 
