@@ -76,6 +76,12 @@ struct psgd_plan {
   int wc_cap = 0;
   int n_max = 0;
   std::vector<int> orth_small, orth_tall, orth_generic;  // K2 routing by row count
+  std::vector<int> orth_tall_s;                          // CTAs cooperating on orth_tall[i] (2 .. orth_tall_cluster)
+  // K2 job tables {matrix, first cluster rank of the group, CTAs in the group, rank in the group} per CTA: the tall
+  // matrices' groups (largest first, so that a group never straddles a hardware cluster) and, in the merged table, the
+  // small matrices behind them
+  std::vector<int4> orth_jobs_tall, orth_jobs_merged;
+  int4 *d_orth_jobs_tall = nullptr, *d_orth_jobs_merged = nullptr;
   int orth_tall_cluster = kOrthCluster;
   int split_max_sub = 0;        // K1: column-split units with at most this many row groups (PSGD_SPLIT_MAX_SUB, 0..3)
   bool pdl = true;              // programmatic dependent launch between the kernels of a step (PSGD_PDL)
@@ -671,9 +677,30 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
     for (int i = 0; i < n_mat; ++i) {
       const long long nn = p->mats[i].n;
       if (nn == 0 || p->mats[i].m == 0) continue;
-      if (R <= 16 && nn <= (long long)orth_threads(R) * rpt) p->orth_small.push_back(i);
-      else if (R <= 16 && nn <= (long long)p->orth_tall_cluster * orth_threads(R) * rpt) p->orth_tall.push_back(i);
+      const long long cap = (long long)orth_threads(R) * rpt;  // rows one CTA holds in registers
+      // CTAs per matrix: as many as it takes to hold the rows, and more while a CTA would keep over 1024 rows (8
+      // warps): a step is paced by the CTA's slowest warp reaching the barrier before warp 0 can send (rank 4: 30
+      // warps per CTA 1.5 us per step, 15 warps 1.15 us; rank 16: 12 warps 1.6 us, 6 warps 1.0 us)
+      int grp = 1;
+      while (((long long)grp * cap < nn || (long long)grp * 1024 < nn) && grp < p->orth_tall_cluster) grp *= 2;
+      if (R <= 16 && nn <= cap) p->orth_small.push_back(i);
+      else if (R <= 16 && nn <= (long long)grp * cap) { p->orth_tall.push_back(i); p->orth_tall_s.push_back(grp); }
       else p->orth_generic.push_back(i);
+    }
+    {  // job tables: groups in descending size (powers of two: every group starts at a multiple of its size)
+      std::vector<int> order(p->orth_tall.size());
+      for (size_t k = 0; k < order.size(); ++k) order[k] = (int)k;
+      std::stable_sort(order.begin(), order.end(), [&](int a, int b) { return p->orth_tall_s[a] > p->orth_tall_s[b]; });
+      const int H = p->orth_tall_cluster;
+      for (int k : order) {
+        const int g = p->orth_tall_s[k], pos = (int)p->orth_jobs_tall.size();
+        for (int c = 0; c < g; ++c) p->orth_jobs_tall.push_back(make_int4(p->orth_tall[k], pos % H, g, c));
+      }
+      p->orth_jobs_merged = p->orth_jobs_tall;
+      for (int i : p->orth_small) {
+        const int pos = (int)p->orth_jobs_merged.size();
+        p->orth_jobs_merged.push_back(make_int4(i, pos % H, 1, 0));
+      }
     }
   }
 
@@ -732,6 +759,8 @@ int psgd_plan_create(int n_mat, const int64_t* n, const int64_t* m, int rank, in
     rc |= upload(&p->d_orth_small, p->orth_small);
     rc |= upload(&p->d_orth_tall, p->orth_tall);
     rc |= upload(&p->d_orth_generic, p->orth_generic);
+    rc |= upload(&p->d_orth_jobs_tall, p->orth_jobs_tall);
+    rc |= upload(&p->d_orth_jobs_merged, p->orth_jobs_merged);
 
     // ring slot: 5 pointer arrays + flags per matrix, 2 pointer arrays per vector
     size_t sb = (size_t)n_mat * (5 * sizeof(void*) + sizeof(unsigned)) + (size_t)n_vec * 4 * sizeof(void*);
@@ -779,6 +808,8 @@ int psgd_plan_destroy(psgd_plan* p) {
     cudaFree(p->d_orth_small);
     cudaFree(p->d_orth_tall);
     cudaFree(p->d_orth_generic);
+    cudaFree(p->d_orth_jobs_tall);
+    cudaFree(p->d_orth_jobs_merged);
     cudaFree(p->d_ring);
     if (p->h_ring) cudaFreeHost(p->h_ring);
     for (int s = 0; s < kSlots; ++s)
@@ -809,7 +840,7 @@ int psgd_tile_count(const psgd_plan* p, int phase) {
     case PSGD_PHASE_P_FROM_M: return (int)p->tiles1.size();
     case PSGD_PHASE_FINALIZE: return (int)p->tiles4.size();
     case PSGD_PHASE_Q_FROM_MT: return (int)p->tiles3.size();
-    case PSGD_PHASE_ORTH: return (int)(p->orth_small.size() + p->orth_tall.size() * p->orth_tall_cluster + p->orth_generic.size() * kOrthCluster);
+    case PSGD_PHASE_ORTH: return (int)(p->orth_jobs_merged.size() + p->orth_generic.size() * kOrthCluster);
     default: return 0;
   }
 }
@@ -1141,8 +1172,8 @@ static int orth_impl(psgd_plan* p, float* p_mem, float n_workers, psgd_stream st
   // lost to cluster placement.
   const int tcs = p->orth_tall_cluster;
   const int n_small = (int)p->orth_small.size(), n_tall = (int)p->orth_tall.size();
-  const bool merged = n_tall > 0 && n_small > 0 && p->orth_merge &&
-                      (n_tall + (n_small + tcs - 1) / tcs) * tcs <= p->orth_merge_max_ctas;
+  const int merged_ctas = ((int)p->orth_jobs_merged.size() + tcs - 1) / tcs * tcs;
+  const bool merged = n_tall > 0 && n_small > 0 && p->orth_merge && merged_ctas <= p->orth_merge_max_ctas;
   // 1. matrices that fit one CTA's registers: one CTA each, block barriers only
   if (n_small && !merged) {
     const unsigned grid = (unsigned)n_small;
@@ -1159,22 +1190,23 @@ static int orth_impl(psgd_plan* p, float* p_mem, float n_workers, psgd_stream st
     const int* d_ids = pass == 0 ? p->d_orth_tall : p->d_orth_generic;
     if (ids.empty()) continue;
     const int csz = pass == 0 ? tcs : kOrthCluster;
-    const int n_ride = (pass == 0 && merged) ? n_small : 0;
-    const dim3 grid((unsigned)(ids.size() + (n_ride + csz - 1) / csz) * csz);
     if (pass == 0) {
-      const int* d_small = p->d_orth_small;
+      const int n_jobs = (int)(merged ? p->orth_jobs_merged.size() : p->orth_jobs_tall.size());
+      const int4* d_jobs = merged ? p->d_orth_jobs_merged : p->d_orth_jobs_tall;
+      const dim3 grid((unsigned)((n_jobs + csz - 1) / csz * csz));
       if (p->R <= 8) {
         DISPATCH_R8(p->R, {
           if (csz > 8 && !p->orth16_attr) CU(cudaFuncSetAttribute((const void*)k_orth_tall<RR, 4>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
           p->orth16_attr = true;
-          CU(launch_ex(k_orth_tall<RR, 4>, grid, dim3(orth_threads(p->R)), 0, s, csz, p->pdl, dp, d_ids, n_tall, d_small, n_ride, p_mem, n_workers));
+          CU(launch_ex(k_orth_tall<RR, 4>, grid, dim3(orth_threads(p->R)), 0, s, csz, p->pdl, dp, d_jobs, n_jobs, p_mem, n_workers));
         });
       } else {
         if (!p->orth16_attr) CU(cudaFuncSetAttribute((const void*)k_orth_tall<16, 4>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
         p->orth16_attr = true;
-        CU(launch_ex(k_orth_tall<16, 4>, grid, dim3(orth_threads(p->R)), 0, s, csz, p->pdl, dp, d_ids, n_tall, d_small, n_ride, p_mem, n_workers));
+        CU(launch_ex(k_orth_tall<16, 4>, grid, dim3(orth_threads(p->R)), 0, s, csz, p->pdl, dp, d_jobs, n_jobs, p_mem, n_workers));
       }
     } else {
+      const dim3 grid((unsigned)ids.size() * csz);
       // the generic kernel has no dependency wait of its own: plain stream order
       DISPATCH_R(p->R, { CU(launch_ex(k_orthogonalize<RR>, grid, dim3(kOrthThreads), 0, s, csz, false, dp, d_ids, p_mem, n_workers)); });
     }
@@ -1543,7 +1575,7 @@ int psgd_orthogonalize_peer(psgd_plan* p, psgd_peer* peer, float* p_mem, float* 
   pf.div = world;
   const int n_flat_ctas = want_flat ? (int)((p->v_total + peer_flat_per_cta(p->R) - 1) / peer_flat_per_cta(p->R)) : 0;
   const int tcs = p->orth_tall_cluster;
-  const bool merged = n_tall > 0 && (n_tall + (n_small + n_flat_ctas + tcs - 1) / tcs) * tcs <= std::max(p->orth_merge_max_ctas, 148);
+  const bool merged = n_tall > 0 && ((int)p->orth_jobs_merged.size() + n_flat_ctas + tcs - 1) / tcs * tcs <= std::max(p->orth_merge_max_ctas, 148);
   if (n_tall == 0 || !merged) {  // small matrices (and, without tall ones, the flat buffer) in a plain launch
     const bool flat_here = n_tall == 0;
     PeerFlat pf_small = flat_here ? pf : PeerFlat{};
@@ -1558,18 +1590,20 @@ int psgd_orthogonalize_peer(psgd_plan* p, psgd_peer* peer, float* p_mem, float* 
     }
   }
   if (n_tall) {
-    const int n_ride = merged ? n_small : 0;
-    const dim3 grid((unsigned)(n_tall + (n_ride + n_flat_ctas + tcs - 1) / tcs) * tcs);
+    // CTAs behind the job table sum the flat buffer
+    const int n_jobs = (int)(merged ? p->orth_jobs_merged.size() : p->orth_jobs_tall.size());
+    const int4* d_jobs = merged ? p->d_orth_jobs_merged : p->d_orth_jobs_tall;
+    const dim3 grid((unsigned)((n_jobs + n_flat_ctas + tcs - 1) / tcs * tcs));
     if (p->R <= 8) {
       DISPATCH_R8(p->R, {
         if (tcs > 8 && !p->orth16_attr_peer) CU(cudaFuncSetAttribute((const void*)k_orth_tall_peer<RR, 4>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
         p->orth16_attr_peer = true;
-        CU(launch_ex(k_orth_tall_peer<RR, 4>, grid, dim3(orth_threads(p->R)), 0, s, tcs, p->pdl, dp, (const int*)p->d_orth_tall, n_tall, (const int*)p->d_orth_small, n_ride, p_mem, world, pm, pf));
+        CU(launch_ex(k_orth_tall_peer<RR, 4>, grid, dim3(orth_threads(p->R)), 0, s, tcs, p->pdl, dp, d_jobs, n_jobs, p_mem, world, pm, pf));
       });
     } else {
       if (!p->orth16_attr_peer) CU(cudaFuncSetAttribute((const void*)k_orth_tall_peer<16, 4>, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
       p->orth16_attr_peer = true;
-      CU(launch_ex(k_orth_tall_peer<16, 4>, grid, dim3(orth_threads(p->R)), 0, s, tcs, p->pdl, dp, (const int*)p->d_orth_tall, n_tall, (const int*)p->d_orth_small, n_ride, p_mem, world, pm, pf));
+      CU(launch_ex(k_orth_tall_peer<16, 4>, grid, dim3(orth_threads(p->R)), 0, s, tcs, p->pdl, dp, d_jobs, n_jobs, p_mem, world, pm, pf));
     }
     if (check_launch("k_orth_tall_peer")) return 1;
   }

@@ -273,7 +273,7 @@ __device__ __forceinline__ void orth_body(float* __restrict__ P, int n, int r, f
 #ifdef PSGD_ORTH_TS
 __device__ unsigned long long g_orth_ts[64][12];
 __device__ __forceinline__ void orth_ts(int slot) {
-  if (threadIdx.x == 0 && blockIdx.x < 64) {
+  if (threadIdx.x == 0 && blockIdx.x < 64 && slot < 12) {
     unsigned long long t;
     asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
     g_orth_ts[blockIdx.x][slot] = t;
@@ -283,6 +283,35 @@ __device__ __forceinline__ void orth_ts(int slot) {
 #else
 #define ORTH_TS(s)
 #endif
+// The step's R sums over the csize partials in `part` ([c][R]), for every thread.  One CTA: read them.  A cluster: the
+// warp shares the work -- lane l adds the partials c = l / R, l / R + 32 / R, ... of value l % R, xor-shuffles join the
+// 32 / R lanes of a value, R more hand every total to every lane -- instead of csize * R additions in every thread
+// (at R = 16 and 16 CTAs those were half of a step's instructions).  Same order in every warp of every CTA.
+template <int R>
+__device__ __forceinline__ void orth_totals(const float* part, int csize, int lane, float (&tot)[R]) {
+  if (csize == 1) {
+    if (R % 4 == 0) {
+#pragma unroll
+      for (int j = 0; j < R; j += 4) {
+        const float4 q = *reinterpret_cast<const float4*>(part + j);
+        tot[j] = q.x; tot[(j + 1) % R] = q.y; tot[(j + 2) % R] = q.z; tot[(j + 3) % R] = q.w;
+      }
+    } else {
+#pragma unroll
+      for (int j = 0; j < R; ++j) tot[j] = part[j];
+    }
+    return;
+  }
+  constexpr int LPV = 32 / R;
+  const int j = lane % R;
+  float x = 0.f;
+  for (int c = lane / R; c < csize; c += LPV) x += part[c * R + j];
+#pragma unroll
+  for (int o = R; o < 32; o <<= 1) x += __shfl_xor_sync(0xffffffffu, x, o);
+#pragma unroll
+  for (int k = 0; k < R; ++k) tot[k] = __shfl_sync(0xffffffffu, x, k);
+}
+
 // Register-resident variant: every thread keeps its (at most RPT) rows in registers for all r steps,
 // so P is read once and written once and a step costs one block (+ cluster) reduction.  csize == 1
 // runs a whole matrix in one CTA with block barriers only; csize > 1 spreads one tall matrix over a
@@ -295,12 +324,14 @@ __device__ __forceinline__ void orth_ts(int slot) {
 // seen all csize partials.  (A cluster-wide barrier after plain remote stores cost 1.05 us per step, twice the step
 // itself.)  `part` and the barriers alternate between two sets: a CTA that is one step ahead writes the other set, and
 // it cannot be two ahead because it needs this CTA's next partial first.
+// The csize cooperating CTAs are the cluster ranks cbase .. cbase + csize - 1 of the hardware cluster (crank counts
+// from cbase): groups smaller than the hardware cluster share one, each exchanging only among its own CTAs.
 // pm != nullptr: the rows are read "summed over all ranks" from symmetric memory (element offset sym_off of the
 // buffer pm describes: the SUM all-reduce of reducer.py:126 happens on load), the result goes to the local P.
 template <int R, int RPT>
 __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r, float world,
                                             int crank, int csize, float* wsum, float* part, uint64_t* cbar,
-                                            const PeerLoad* pm = nullptr, long long sym_off = 0) {
+                                            const PeerLoad* pm = nullptr, long long sym_off = 0, int cbase = 0) {
   constexpr int LPV = 32 / R;  // lanes per value after a warp_fold<R>
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int per = (n + csize - 1) / csize;
@@ -382,7 +413,7 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
           const int j = lane / LPV;
           const uint32_t slot = smem_u32(part + (par * kOrthClusterMax + crank) * R + j), bar = smem_u32(&cbar[par]);
           for (int dst = lane % LPV; dst < csize; dst += LPV)
-            st_async_f32(cluster_map_u32(slot, dst), w, cluster_map_u32(bar, dst));
+            st_async_f32(cluster_map_u32(slot, cbase + dst), w, cluster_map_u32(bar, cbase + dst));
           if (lane == 0) mbar_arrive_expect_tx(&cbar[par], (uint32_t)csize * R * 4u);
         } else if ((lane % LPV) == 0) {
           part[(par * kOrthClusterMax) * R + lane / LPV] = w;
@@ -390,20 +421,7 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
       }
       if (csize > 1) mbar_wait_lite(&cbar[par], (uint32_t)(i >> 1) & 1u); else cta_sync();
       float tot[R];
-#pragma unroll
-      for (int j = 0; j < R; ++j) tot[j] = 0.f;
-      for (int c = 0; c < csize; ++c) {
-        if (R % 4 == 0) {
-#pragma unroll
-          for (int j = 0; j < R; j += 4) {
-            const float4 q = *reinterpret_cast<const float4*>(part + (par * kOrthClusterMax + c) * R + j);
-            tot[j] += q.x; tot[(j + 1) % R] += q.y; tot[(j + 2) % R] += q.z; tot[(j + 3) % R] += q.w;
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < R; ++j) tot[j] += part[(par * kOrthClusterMax + c) * R + j];
-        }
-      }
+      orth_totals<R>(part + par * kOrthClusterMax * R, csize, lane, tot);
       const float inv = 1.0f / (sqrtf(tot[0]) + 1e-8f);  // eps outside the root, reducer.py:186
       const int live = R - i;  // positions 1 .. live-1 hold the columns still to be projected
 #pragma unroll
@@ -456,7 +474,7 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
           const int j = lane / LPV;
           const uint32_t slot = smem_u32(part + (par * kOrthClusterMax + crank) * R + j), bar = smem_u32(&cbar[par]);
           for (int dst = lane % LPV; dst < csize; dst += LPV)
-            st_async_f32(cluster_map_u32(slot, dst), w, cluster_map_u32(bar, dst));
+            st_async_f32(cluster_map_u32(slot, cbase + dst), w, cluster_map_u32(bar, cbase + dst));
           if (lane == 0) mbar_arrive_expect_tx(&cbar[par], (uint32_t)csize * R * 4u);
         } else if ((lane % LPV) == 0) {
           part[(par * kOrthClusterMax) * R + lane / LPV] = w;
@@ -464,20 +482,7 @@ __device__ __forceinline__ void orth_cached(float* __restrict__ P, int n, int r,
       }
       if (csize > 1) mbar_wait_lite(&cbar[par], (uint32_t)(i >> 1) & 1u); else cta_sync();
       float tot[R];
-#pragma unroll
-      for (int j = 0; j < R; ++j) tot[j] = 0.f;
-      for (int c = 0; c < csize; ++c) {
-        if (R % 4 == 0) {
-#pragma unroll
-          for (int j = 0; j < R; j += 4) {
-            const float4 q = *reinterpret_cast<const float4*>(part + (par * kOrthClusterMax + c) * R + j);
-            tot[j] += q.x; tot[(j + 1) % R] += q.y; tot[(j + 2) % R] += q.z; tot[(j + 3) % R] += q.w;
-          }
-        } else {
-#pragma unroll
-          for (int j = 0; j < R; ++j) tot[j] += part[(par * kOrthClusterMax + c) * R + j];
-        }
-      }
+      orth_totals<R>(part + par * kOrthClusterMax * R, csize, lane, tot);
       const float inv = 1.0f / (sqrtf(tot[i]) + 1e-8f);  // eps outside the root, reducer.py:186
       float coef[R];
 #pragma unroll
@@ -578,70 +583,49 @@ k_orth_small_peer(DevPlan pl, const int* __restrict__ ids, int n_small, float* _
   }
 }
 
-// one cluster per "tall" matrix (n <= cluster * blockDim * RPT).  When the plan also has small matrices and everything
-// fits one wave, they ride on the same launch: the clusters behind the n_tall cooperative ones are mere containers whose
-// CTAs each take one small matrix and never touch the cluster barrier.
+// Matrices too tall for one CTA, each on a group of 2, 4, 8 or 16 CTAs (n <= group * blockDim * RPT) of a 16-CTA
+// hardware cluster, per the plan's job table {matrix, first cluster rank of the group, CTAs in the group, rank in the
+// group}.  When the plan also has small matrices and everything fits one wave, they ride on the same launch as groups
+// of one.  CTAs past the table have nothing to do.
 template <int R, int RPT>
 __global__ void __launch_bounds__(orth_threads(R))
-k_orth_tall(DevPlan pl, const int* __restrict__ ids, int n_tall, const int* __restrict__ small_ids, int n_small,
-            float* __restrict__ p_mem, float world) {
+k_orth_tall(DevPlan pl, const int4* __restrict__ jobs, int n_jobs, float* __restrict__ p_mem, float world) {
   __shared__ __align__(16) float wsum[32 * R];
   __shared__ __align__(16) float part[2 * kOrthClusterMax * R];
-  cg::cluster_group cluster = cg::this_cluster();
-  const int csize = (int)cluster.num_blocks();
-  const int cl = blockIdx.x / csize;
   __shared__ uint64_t cbar[2];
   ORTH_TS(0);
   pdl_launch_dependents();
-  if (cl < n_tall) {
-    const int mat = ids[cl];
-    const MatDesc md = pl.mats[mat];
-    orth_cluster_init(cbar);  // under the predecessor's tail
-    pdl_wait();
-    ORTH_TS(1);
-    orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, (int)cluster.block_rank(), csize, wsum, part, cbar);
-  } else {
-    const int idx = (cl - n_tall) * csize + (int)cluster.block_rank();
-    if (idx >= n_small) {
-      pdl_wait();  // every CTA waits: the grid must not be able to complete before its predecessor has
-      return;
-    }
-    const int mat = small_ids[idx];
-    const MatDesc md = pl.mats[mat];
-    pdl_wait();
-    ORTH_TS(1);
-    orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, 0, 1, wsum, part, nullptr);
+  orth_cluster_init(cbar);  // every CTA of every cluster; under the predecessor's tail
+  if ((int)blockIdx.x >= n_jobs) {
+    pdl_wait();  // every CTA waits: the grid must not be able to complete before its predecessor has
+    return;
   }
+  const int4 job = jobs[blockIdx.x];
+  const MatDesc md = pl.mats[job.x];
+  pdl_wait();
+  ORTH_TS(1);
+  orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, job.w, job.z, wsum, part, cbar, nullptr, 0, job.y);
 }
 
-// tall matrices one cluster each, small ones in container clusters, then the flat buffer (see k_orth_small_peer)
+// the same with the P all-reduce on load; CTAs past the job table sum the flat buffer (see k_orth_small_peer)
 template <int R, int RPT>
 __global__ void __launch_bounds__(orth_threads(R))
-k_orth_tall_peer(DevPlan pl, const int* __restrict__ ids, int n_tall, const int* __restrict__ small_ids, int n_small,
-                 float* __restrict__ p_mem, float world, PeerLoad pm, PeerFlat pf) {
+k_orth_tall_peer(DevPlan pl, const int4* __restrict__ jobs, int n_jobs, float* __restrict__ p_mem, float world,
+                 PeerLoad pm, PeerFlat pf) {
   __shared__ __align__(16) float wsum[32 * R];
   __shared__ __align__(16) float part[2 * kOrthClusterMax * R];
-  cg::cluster_group cluster = cg::this_cluster();
-  const int csize = (int)cluster.num_blocks();
-  const int cl = blockIdx.x / csize;
   __shared__ uint64_t cbar[2];
   pdl_launch_dependents();
-  if (cl < n_tall) orth_cluster_init(cbar);  // under the predecessor's tail
+  orth_cluster_init(cbar);  // every CTA of every cluster; under the predecessor's tail
+  const bool has_job = (int)blockIdx.x < n_jobs;
+  const int4 job = has_job ? jobs[blockIdx.x] : make_int4(0, 0, 1, 0);
+  const MatDesc md = pl.mats[job.x];  // plan constants: not behind the dependency wait
   pdl_wait();
   peer_barrier(pm, blockIdx.x == 0);
-  if (cl < n_tall) {
-    const int mat = ids[cl];
-    const MatDesc md = pl.mats[mat];
-    orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, (int)cluster.block_rank(), csize, wsum, part, cbar, &pm, md.p_off);
-  } else {
-    const int idx = (cl - n_tall) * csize + (int)cluster.block_rank();
-    if (idx < n_small) {
-      const int mat = small_ids[idx];
-      const MatDesc md = pl.mats[mat];
-      orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, 0, 1, wsum, part, nullptr, &pm, md.p_off);
-    } else if (pf.out) {
-      peer_flat_job(pm, pf, idx - n_small);
-    }
+  if (has_job) {
+    orth_cached<R, RPT>(p_mem + md.p_off, md.n, md.r, world, job.w, job.z, wsum, part, cbar, &pm, md.p_off, job.y);
+  } else if (pf.out) {
+    peer_flat_job(pm, pf, (int)blockIdx.x - n_jobs);
   }
 }
 
