@@ -14,8 +14,8 @@ constexpr int kOrthSmallThreads = 1024;  // CTA size of the register-resident Gr
 // At R = 16 the same kernels run 512 threads x 4 rows (same rows per CTA): 128 registers per thread leave room for the
 // rolled step loop with rotating columns; the unrolled 1024 x 2 form spent its time fetching instructions (K2 118 us).
 __host__ __device__ constexpr int orth_threads(int R) { return R >= 16 ? 512 : kOrthSmallThreads; }
-constexpr int kOrthCluster = 8;    // CTAs per matrix (one thread-block cluster)
-constexpr int kOrthClusterMax = 16;  // non-portable cluster size used for tall matrices at R = 16
+constexpr int kOrthCluster = 8;    // portable cluster size: the generic Gram-Schmidt kernel, and K2's fallback hardware cluster
+constexpr int kOrthClusterMax = 16;  // non-portable cluster size: K2's hardware clusters (groups of 1-16 CTAs per matrix inside)
 
 // per-matrix constants, uploaded once per plan
 struct MatDesc {
