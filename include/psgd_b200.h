@@ -70,7 +70,9 @@ int64_t psgd_workspace_bytes(const psgd_plan* plan); /* scratch for psgd_q_from_
 /* out[0..7] = n, m, r, p_off, q_off, ws_off, k3 row blocks, k3 columns per tile */
 int psgd_matrix_info(const psgd_plan* plan, int i, int64_t* out8);
 int psgd_tile_count(const psgd_plan* plan, int phase);
-/* out[0..5] = matrix, row0, nrows, col0, ncols, row-block index */
+/* out[0..5] = matrix, row0, nrows, col0, ncols, row-block index.
+ * PSGD_PHASE_ORTH: the Gram-Schmidt job of CTA idx -- matrix, first cluster rank of the group of CTAs that shares the
+ * matrix, CTAs in the group, this CTA's rank in the group, CTAs per hardware cluster, 1 for the generic kernel. */
 int psgd_tile_get(const psgd_plan* plan, int phase, int idx, int32_t* out6);
 
 /* Per-step pointer refresh: parameter.grad is re-allocated by zero_grad()

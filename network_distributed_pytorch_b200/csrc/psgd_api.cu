@@ -855,6 +855,18 @@ int psgd_tile_get(const psgd_plan* p, int phase, int idx, int32_t* o) {
     const MatDesc& md = p->mats[t.mat];
     o[0] = t.mat; o[1] = t.row0; o[2] = t.nrows; o[3] = t.col0;
     o[4] = std::min(md.cgw * md.cpt, md.m - t.col0); o[5] = t.blk;
+  } else if (phase == PSGD_PHASE_ORTH) {
+    // K2 job of CTA idx of the merged launch: {matrix, first cluster rank of its group, CTAs in the group, rank in
+    // the group, CTAs per hardware cluster, 0}; behind them the matrices of the generic kernel (one 8-CTA cluster each)
+    const int nj = (int)p->orth_jobs_merged.size();
+    if (idx < nj) {
+      const int4 j = p->orth_jobs_merged[idx];
+      o[0] = j.x; o[1] = j.y; o[2] = j.z; o[3] = j.w; o[4] = p->orth_tall_cluster; o[5] = 0;
+    } else {
+      const int k = idx - nj;
+      o[0] = p->orth_generic[k / kOrthCluster]; o[1] = 0; o[2] = kOrthCluster; o[3] = k % kOrthCluster;
+      o[4] = kOrthCluster; o[5] = 1;
+    }
   } else {
     return fail("psgd_tile_get: phase %d has no tile table", phase);
   }

@@ -128,6 +128,43 @@ def test_packed_layout_and_tiles(lib, name, rank):
     assert plan.workspace_bytes >= 4 * ws_end
 
 
+@pytest.mark.parametrize("name,rank", [("distilbert", 4), ("distilbert", 8), ("distilbert", 16), ("bert-large", 8),
+                                       ("resnet50", 4), ("tall_mix", 4), ("tall_mix", 16)])
+def test_gram_schmidt_job_table(lib, name, rank):
+    """K2's plan-time routing: every matrix is orthogonalised by exactly one group of CTAs; groups are powers of two,
+    start at a multiple of their size inside a hardware cluster (so they never straddle one), hold all rows of their
+    matrix in registers (4 rows per thread) and no CTA of a group keeps more than 1024 rows unless the group already
+    is a whole cluster; a matrix too tall for a whole cluster goes to the generic kernel."""
+    if name == "tall_mix":
+        mats = [(4096, 8), (4097, 8), (9000, 8), (30522, 8), (65536, 8), (65537, 8), (3, 8), (2049, 8)]
+    else:
+        mats, _ = split(workloads.WORKLOADS[name]())
+    plan = host_plan(mats, rank, [])
+    R = 1
+    while R < min(rank, max(min(n, m) for n, m in mats)):
+        R *= 2
+    threads = 512 if R >= 16 else 1024
+    jobs = plan.tiles(_lib.PHASE_ORTH)
+    groups = {}
+    for pos, (mat, cbase, gsize, grank, cluster, generic) in enumerate(jobs):
+        groups.setdefault(mat, []).append((pos, cbase, gsize, grank, cluster, generic))
+    assert sorted(groups) == [i for i, (n, m) in enumerate(mats) if n and m]
+    for mat, ctas in groups.items():
+        n = mats[mat][0]
+        pos0, cbase, gsize, _, cluster, generic = ctas[0]
+        assert len(ctas) == gsize and [c[3] for c in ctas] == list(range(gsize))
+        assert all(c[1] == cbase and c[2] == gsize and c[4] == cluster and c[5] == generic for c in ctas)
+        if generic:
+            assert n > cluster * 2 * threads * 4 or R > 16  # nothing register-resident could have taken it
+            continue
+        assert [c[0] for c in ctas] == list(range(pos0, pos0 + gsize))  # consecutive CTAs of the launch
+        assert gsize & (gsize - 1) == 0 and cbase % gsize == 0 and cbase + gsize <= cluster
+        assert pos0 % cluster == cbase
+        per_cta = -(-n // gsize)
+        assert per_cta <= threads * 4
+        assert per_cta <= 1024 or gsize == cluster or n <= threads * 4 and gsize == 1
+
+
 def test_ragged_and_degenerate_shapes(lib):
     mats = [(1, 5), (5, 1), (64, 147), (3, 7), (1000, 12), (2, 4096 * 3)]
     plan = host_plan(mats, 4, [1, 7])
